@@ -1,0 +1,304 @@
+/*
+ * oracle/bfs_oracle.c — TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * CPU restatement, in plain C, of the reference's hot path:
+ *   edge-list text -> symmetrised CSR -> serial BFS depth array.
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+ * load this file's shared library; the product library (libb2bfs.so) never does.
+ *
+ * Parity status: PINNED.  Every function here is checked in tests/test_oracle.py against the
+ * reference's own host code (readGraphFromFile + bfsCPU, /root/reference/bfs.cu) compiled unmodified
+ * into oracle/_ref/libref_oracle.so, and against the golden vectors under tests/golden/ that were
+ * generated from that library by tests/golden/make_golden.py.
+ *
+ * All citations are into /root/reference/.
+ */
+#include <limits.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../include/b2bfs_graphgen.h"
+
+#define ORACLE_OK 0
+#define ORACLE_ERR_IO -1
+#define ORACLE_ERR_FORMAT -2
+#define ORACLE_ERR_RANGE -3
+#define ORACLE_ERR_NOMEM -4
+
+/* ---------------------------------------------------------------------------------------------
+ * Edge-list text reader.  Follows readGraphFromFile, bfs.cu:829-863: `f >> n >> m`, then m pairs
+ * `f >> u >> v` of whitespace-separated decimal ints, 0-based.  The reference does not check that
+ * the file holds m pairs or that ids are < n (defect D4 in SURVEY.md); the oracle reports those
+ * cases as errors instead of reading uninitialised memory.
+ * Two-call protocol: first with src==dst==NULL to learn n and m, then with buffers of m ints.
+ * ------------------------------------------------------------------------------------------- */
+int oracle_read_edge_file(const char* path, int64_t* n_out, int64_t* m_out, int32_t* src, int32_t* dst) {
+  FILE* f = fopen(path, "r");
+  if (!f) return ORACLE_ERR_IO;
+  long long n, m;
+  if (fscanf(f, "%lld %lld", &n, &m) != 2 || n < 0 || m < 0) { fclose(f); return ORACLE_ERR_FORMAT; }
+  *n_out = n;
+  *m_out = m;
+  if (!src || !dst) { fclose(f); return ORACLE_OK; }
+  for (long long i = 0; i < m; ++i) {
+    long long u, v;
+    if (fscanf(f, "%lld %lld", &u, &v) != 2) { fclose(f); return ORACLE_ERR_FORMAT; }
+    if (u < 0 || v < 0 || u >= n || v >= n) { fclose(f); return ORACLE_ERR_RANGE; }
+    src[i] = (int32_t)u;
+    dst[i] = (int32_t)v;
+  }
+  fclose(f);
+  return ORACLE_OK;
+}
+
+/* Writer for the same format (README.md:8-12): "n m" then one "u v" per line. */
+int oracle_write_edge_file(const char* path, int64_t n, int64_t m, const int32_t* src, const int32_t* dst) {
+  FILE* f = fopen(path, "w");
+  if (!f) return ORACLE_ERR_IO;
+  fprintf(f, "%lld %lld\n", (long long)n, (long long)m);
+  for (int64_t i = 0; i < m; ++i) fprintf(f, "%d %d\n", src[i], dst[i]);
+  return fclose(f) == 0 ? ORACLE_OK : ORACLE_ERR_IO;
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * CSR construction.  Follows bfs.cu:851-875: for every tuple in file order push v onto u's list
+ * and u onto v's list (duplicates kept; a self-loop u==u is pushed twice), then flatten rows in
+ * vertex order into adjacencyList with edgesOffset[v] / edgesSize[v].  A counting pass + cursor
+ * scatter in file order reproduces the per-row push_back order exactly.
+ * offsets has n entries (like edgesOffset), sizes has n entries, adj has 2*m entries.
+ * 64-bit offsets so the restatement also covers E >= 2^31 (the reference overflows there, D3).
+ * ------------------------------------------------------------------------------------------- */
+int oracle_build_csr(int64_t n, int64_t m, const int32_t* src, const int32_t* dst, int64_t* offsets,
+                     int32_t* sizes, int32_t* adj) {
+  memset(sizes, 0, (size_t)n * sizeof(int32_t));
+  for (int64_t i = 0; i < m; ++i) {
+    if (src[i] < 0 || dst[i] < 0 || src[i] >= n || dst[i] >= n) return ORACLE_ERR_RANGE;
+    sizes[src[i]]++;
+    sizes[dst[i]]++;
+  }
+  int64_t run = 0;
+  for (int64_t v = 0; v < n; ++v) { offsets[v] = run; run += sizes[v]; }
+  int64_t* cur = (int64_t*)malloc((size_t)(n > 0 ? n : 1) * sizeof(int64_t));
+  if (!cur) return ORACLE_ERR_NOMEM;
+  memcpy(cur, offsets, (size_t)n * sizeof(int64_t));
+  for (int64_t i = 0; i < m; ++i) {
+    const int32_t u = src[i], v = dst[i];
+    adj[cur[u]++] = v; /* bfs.cu:860 */
+    adj[cur[v]++] = u; /* bfs.cu:861 */
+  }
+  free(cur);
+  return ORACLE_OK;
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * Serial BFS.  Follows bfsCPU, bfs.cu:923-945: FIFO queue, distance[start]=0, parent[start]=start,
+ * first discovery wins, parent[v] = index i of the discovering entry in adjacencyList (NOT a vertex
+ * id).  depth/parent must be pre-filled by the caller with INT_MAX as main does (bfs.cu:793-794);
+ * oracle_bfs_serial does that fill itself for convenience.  parent_edge is int64 so the restatement
+ * holds beyond 2^31 entries; below that it equals the reference's int value.
+ * Returns the number of vertices reached.
+ * ------------------------------------------------------------------------------------------- */
+int64_t oracle_bfs_serial(int64_t n, const int64_t* offsets, const int32_t* sizes, const int32_t* adj,
+                          int64_t start, int32_t* depth, int64_t* parent_edge) {
+  for (int64_t v = 0; v < n; ++v) depth[v] = INT_MAX;
+  if (parent_edge) for (int64_t v = 0; v < n; ++v) parent_edge[v] = INT_MAX;
+  if (start < 0 || start >= n) return ORACLE_ERR_RANGE;
+  uint8_t* visited = (uint8_t*)calloc((size_t)n, 1);
+  int32_t* q = (int32_t*)malloc((size_t)n * sizeof(int32_t));
+  if (!visited || !q) { free(visited); free(q); return ORACLE_ERR_NOMEM; }
+  int64_t head = 0, tail = 0;
+  depth[start] = 0;
+  if (parent_edge) parent_edge[start] = start; /* bfs.cu:926 */
+  visited[start] = 1;
+  q[tail++] = (int32_t)start;
+  while (head < tail) {
+    const int32_t u = q[head++];
+    const int64_t b = offsets[u], e = b + sizes[u];
+    for (int64_t i = b; i < e; ++i) { /* bfs.cu:935 */
+      const int32_t v = adj[i];
+      if (!visited[v]) {
+        visited[v] = 1;
+        depth[v] = depth[u] + 1;
+        if (parent_edge) parent_edge[v] = i; /* bfs.cu:940 */
+        q[tail++] = v;
+      }
+    }
+  }
+  free(visited);
+  free(q);
+  return tail;
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * K-device emulation of the reference's multi-GPU protocol — runCudaQueueBfs bfs.cu:569-619 (and the
+ * 2-rank MPI loop bfs_mpi.cu:581-634) plus the min-merge gather bfs.cu:424-441 / bfs_mpi.cu:424-448.
+ * Each emulated device has a PRIVATE full-length distance array and claims with "== INT_MAX then
+ * min" (queueBfs, bfs.cu:146); discovered ids are bucketed by owner `v / part` (bfs.cu:148) with
+ * part = n / k; the owner appends what every device sent it, in device order (bfs.cu:595-609);
+ * nothing marks the owner's own distance array on receipt, so duplicates may re-enter queues; the
+ * loop ends when all queues are empty (bfs.cu:569 / bfs_mpi.cu:621); the result is the element-wise
+ * min over devices (bfs.cu:430-438).  Requires n % k == 0 (the reference writes out of bounds
+ * otherwise, defect D2).  Within a device the frontier is processed sequentially in queue order,
+ * one legal schedule of the kernel's threads; depths do not depend on the schedule.
+ * Returns the number of levels executed, or a negative error.
+ * ------------------------------------------------------------------------------------------- */
+int64_t oracle_bfs_kdev(int64_t n, const int64_t* offsets, const int32_t* sizes, const int32_t* adj,
+                        int64_t start, int k, int32_t* depth_out) {
+  if (k < 1 || n % k != 0 || start < 0 || start >= n) return ORACLE_ERR_RANGE;
+  const int64_t part = n / k;
+  int32_t** dist = (int32_t**)calloc((size_t)k, sizeof(int32_t*));
+  int32_t** curq = (int32_t**)calloc((size_t)k, sizeof(int32_t*));
+  int32_t** nextq = (int32_t**)calloc((size_t)k, sizeof(int32_t*)); /* k buckets of n ints per device */
+  int64_t* qsize = (int64_t*)calloc((size_t)k, sizeof(int64_t));
+  int64_t* nsize = (int64_t*)calloc((size_t)k * k, sizeof(int64_t));
+  size_t curcap = (size_t)n * (size_t)k + 1; /* an owner can receive up to n ids from each device */
+  for (int d = 0; d < k; ++d) {
+    dist[d] = (int32_t*)malloc((size_t)n * sizeof(int32_t));
+    curq[d] = (int32_t*)malloc(curcap * sizeof(int32_t));
+    nextq[d] = (int32_t*)malloc((size_t)n * (size_t)k * sizeof(int32_t) + 4);
+    for (int64_t v = 0; v < n; ++v) dist[d][v] = INT_MAX; /* bfs.cu:404 */
+    dist[d][start] = 0;                                   /* bfs.cu:406, copied to every device 411 */
+  }
+  const int owner = (int)(start / part); /* getDev, bfs.cu:29-32 */
+  curq[owner][0] = (int32_t)start;
+  qsize[owner] = 1;
+  int64_t level = 0;
+  for (;;) {
+    int64_t total = 0;
+    for (int d = 0; d < k; ++d) total += qsize[d];
+    if (total == 0) break;
+    for (int d = 0; d < k; ++d) { /* queueBfs on device d, bfs.cu:134-165 */
+      for (int64_t t = 0; t < qsize[d]; ++t) {
+        const int32_t u = curq[d][t];
+        const int64_t b = offsets[u], e = b + sizes[u];
+        for (int64_t i = b; i < e; ++i) {
+          const int32_t v = adj[i];
+          if (dist[d][v] == INT_MAX) {
+            dist[d][v] = (int32_t)(level + 1);
+            const int which = (int)(v / part);
+            const int64_t pos = nsize[(size_t)d * k + which]++;
+            nextq[d][pos + (int64_t)which * n] = v;
+          }
+        }
+      }
+    }
+    level++;
+    for (int i = 0; i < k; ++i) { /* exchange, bfs.cu:595-609 */
+      int64_t off = 0;
+      for (int j = 0; j < k; ++j) {
+        const int64_t c = nsize[(size_t)j * k + i];
+        memcpy(curq[i] + off, nextq[j] + (int64_t)i * n, (size_t)c * sizeof(int32_t));
+        off += c;
+      }
+      qsize[i] = off; /* bfs.cu:617-618 */
+    }
+    memset(nsize, 0, (size_t)k * k * sizeof(int64_t)); /* bfs.cu:619 */
+  }
+  for (int64_t v = 0; v < n; ++v) { /* finalizeCudaBfs min-merge, bfs.cu:430-438 */
+    int32_t best = dist[0][v];
+    for (int d = 1; d < k; ++d) if (dist[d][v] < best) best = dist[d][v];
+    depth_out[v] = best;
+  }
+  for (int d = 0; d < k; ++d) { free(dist[d]); free(curq[d]); free(nextq[d]); }
+  free(dist); free(curq); free(nextq); free(qsize); free(nsize);
+  return level;
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * checkOutput, bfs.cu:374-384: first index where two depth arrays differ, or -1 ("Output OK!").
+ * ------------------------------------------------------------------------------------------- */
+int64_t oracle_check_output(int64_t n, const int32_t* got, const int32_t* expected) {
+  for (int64_t i = 0; i < n; ++i)
+    if (got[i] != expected[i]) return i;
+  return -1;
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * Synthetic inputs: tuples [first, first+count) of the generator defined in
+ * include/b2bfs_graphgen.h.  No reference counterpart (the reference ships no live generator).
+ * ------------------------------------------------------------------------------------------- */
+void oracle_generate_edges(int kind, int scale, int edgefactor, uint64_t seed, int64_t first, int64_t count,
+                           int32_t* src, int32_t* dst) {
+  for (int64_t i = 0; i < count; ++i) {
+    uint32_t u, v;
+    b2_gen_edge(kind, scale, edgefactor, seed, (uint64_t)(first + i), &u, &v);
+    src[i] = (int32_t)u;
+    dst[i] = (int32_t)v;
+  }
+}
+int64_t oracle_gen_num_vertices(int kind, int scale) { return b2_gen_num_vertices(kind, scale); }
+int64_t oracle_gen_num_edges(int kind, int scale, int ef) { return b2_gen_num_edges(kind, scale, ef); }
+
+/* ---------------------------------------------------------------------------------------------
+ * Graph500 BFS-tree validation (the five rules of the Graph500 specification, "kernel 2
+ * validation"), stated over the reference's symmetrised multigraph CSR.  parent[] holds VERTEX ids
+ * (root -> root, -1 = not reached) as exported by the product's ABI; depth[] is the level array
+ * with INT_MAX = not reached.  The reference itself never validates parents (bfs.cu:374-384
+ * compares depth only), so this has no reference counterpart.
+ * Returns 0 when valid, otherwise a positive rule number; *bad_vertex gets an offending vertex.
+ *   1 root is its own parent with depth 0
+ *   2 every reached non-root vertex has a reached parent exactly one level closer, and the pair
+ *     (v, parent[v]) is an edge of the input graph
+ *   3 every input edge joins vertices whose levels differ by at most one, or two unreached ones
+ *   4 reached <=> has a parent (the tree spans exactly the root's component; with rule 3 no edge
+ *     leaves the reached set)
+ *   5 depth array equals the level implied by walking parents (no cycles)
+ * ------------------------------------------------------------------------------------------- */
+int oracle_validate_tree(int64_t n, const int64_t* offsets, const int32_t* sizes, const int32_t* adj,
+                         int64_t root, const int32_t* depth, const int32_t* parent, int64_t* bad_vertex) {
+  int64_t dummy;
+  if (!bad_vertex) bad_vertex = &dummy;
+  *bad_vertex = root;
+  if (root < 0 || root >= n || parent[root] != root || depth[root] != 0) return 1;
+  for (int64_t v = 0; v < n; ++v) {
+    *bad_vertex = v;
+    const int reached = depth[v] != INT_MAX;
+    if (reached != (parent[v] >= 0)) return 4;
+    if (!reached || v == root) continue;
+    const int32_t p = parent[v];
+    if (depth[v] < 1) return 5; /* only the root sits at level 0 */
+    if (p >= n || depth[p] == INT_MAX || depth[p] != depth[v] - 1) return 2;
+    int found = 0;
+    for (int64_t i = offsets[v], e = offsets[v] + sizes[v]; i < e; ++i)
+      if (adj[i] == p) { found = 1; break; }
+    if (!found) return 2;
+  }
+  for (int64_t v = 0; v < n; ++v) {
+    *bad_vertex = v;
+    for (int64_t i = offsets[v], e = offsets[v] + sizes[v]; i < e; ++i) {
+      const int32_t w = adj[i];
+      const int rv = depth[v] != INT_MAX, rw = depth[w] != INT_MAX;
+      if (rv != rw) return 3;
+      if (rv) {
+        const int32_t d = depth[v] - depth[w];
+        if (d > 1 || d < -1) return 3;
+      }
+    }
+  }
+  /* rule 5 follows by induction from rule 2 + "depth >= 1 off the root"; the explicit walk is kept
+     for small graphs as a belt-and-braces check (it is O(n * depth)). */
+  for (int64_t v = 0; v < n && n <= (1 << 20); ++v) {
+    if (depth[v] == INT_MAX) continue;
+    *bad_vertex = v;
+    int64_t x = v;
+    int32_t steps = 0;
+    while (x != root && steps <= depth[v]) { x = parent[x]; ++steps; }
+    if (x != root || steps != depth[v]) return 5;
+  }
+  *bad_vertex = -1;
+  return 0;
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * Bookkeeping for the metric: reached vertices V_r and reached directed entries
+ * D_r = sum of edgesSize over reached vertices = 2*m_r on the reference's CSR.
+ * ------------------------------------------------------------------------------------------- */
+void oracle_reach_stats(int64_t n, const int32_t* sizes, const int32_t* depth, int64_t* v_r, int64_t* d_r) {
+  int64_t vr = 0, dr = 0;
+  for (int64_t v = 0; v < n; ++v)
+    if (depth[v] != INT_MAX) { vr++; dr += sizes[v]; }
+  *v_r = vr;
+  *d_r = dr;
+}

@@ -1,0 +1,190 @@
+"""CPU tests: the oracle (oracle/bfs_oracle.c) against the golden vectors that the reference's own host
+code produced (tests/golden/make_golden.py), against the reference library itself where it is
+present (oracle/_ref, build container only), and against scipy as an independent third opinion."""
+import os
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+from scipy.sparse.csgraph import shortest_path
+
+import oracle
+from conftest import golden_names, load_golden
+
+INT_MAX = oracle.INT_MAX
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_oracle_matches_reference_golden(name):
+    path, gold = load_golden(name)
+    n, src, dst = oracle.read_edge_file(path)
+    assert n == gold["n"] and len(src) == gold["m"]
+    g = oracle.build_csr(n, src, dst)
+    assert g.num_edges == gold["num_edges_printed"] == 2 * gold["m"]  # bfs.cu:875
+    if gold["adj"] is not None:
+        assert g.offsets.tolist() == gold["offsets"]
+        assert g.sizes.tolist() == gold["sizes"]
+        assert g.adj.tolist() == gold["adj"]
+    chk = int((g.adj.astype(np.int64) * (np.arange(g.adj.size) % 1000003 + 1)).sum() % (2**61 - 1))
+    assert chk == gold["csr_checksum"]
+    for s in gold["searches"]:
+        depth, parent = oracle.bfs_serial(g, s["root"], want_parent=True)
+        assert oracle.check_output(depth, np.array(s["depth"], np.int32)) == -1
+        assert parent.tolist() == s["parent_edge"]  # edge indices, bfs.cu:940
+
+
+def test_survey_golden_vector():
+    # the vector obtained from the reference's host code during the survey
+    path, _ = load_golden("tiny")
+    n, src, dst = oracle.read_edge_file(path)
+    g = oracle.build_csr(n, src, dst)
+    assert g.offsets.tolist() == [0, 2, 5, 7, 10, 10]
+    assert g.sizes.tolist() == [2, 3, 2, 3, 0, 0]
+    assert g.adj.tolist() == [1, 1, 0, 2, 0, 1, 3, 2, 3, 3]
+    depth, parent = oracle.bfs_serial(g, 2, want_parent=True)
+    assert depth.tolist() == [2, 1, 0, 1, INT_MAX, INT_MAX]
+    assert parent.tolist() == [2, 5, 2, 6, INT_MAX, INT_MAX]
+
+
+@pytest.mark.skipif(not oracle.ref_available(), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("kind,scale,seed", [(oracle.GEN_RMAT, 10, 1), (oracle.GEN_KRON, 10, 7), (oracle.GEN_GRID, 10, 0)])
+def test_oracle_matches_reference_library(tmp_path, kind, scale, seed):
+    """Live comparison with the reference's loader and bfsCPU, through a real text file."""
+    n, src, dst = oracle.generate_edges(kind, scale, 16, seed)
+    path = str(tmp_path / "g.txt")
+    oracle.write_edge_file(path, n, src, dst)
+    gr = oracle.ref_load_file(path)
+    n2, s2, d2 = oracle.read_edge_file(path)
+    g = oracle.build_csr(n2, s2, d2)
+    assert np.array_equal(g.offsets, gr.offsets) and np.array_equal(g.sizes, gr.sizes) and np.array_equal(g.adj, gr.adj)
+    for root in (2, 0, n - 1, n // 2):
+        dr, pr, _ = oracle.ref_bfs_cpu(root, n, want_parent=True)
+        do, po = oracle.bfs_serial(g, root, want_parent=True)
+        assert oracle.check_output(do, dr) == -1
+        assert np.array_equal(po.astype(np.int32), pr)
+
+
+@pytest.mark.skipif(not oracle.ref_available(), reason="oracle/_ref not built")
+def test_ref_set_graph_equals_file_load(tmp_path):
+    n, src, dst = oracle.generate_edges(oracle.GEN_RMAT, 9, 8, 3)
+    g = oracle.build_csr(n, src, dst)
+    oracle.ref_set_graph(g)
+    d1, _ = oracle.ref_bfs_cpu(2, n)
+    path = str(tmp_path / "g.txt")
+    oracle.write_edge_file(path, n, src, dst)
+    oracle.ref_load_file(path)
+    d2, _ = oracle.ref_bfs_cpu(2, n)
+    assert np.array_equal(d1, d2)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_oracle_vs_scipy(seed):
+    rng = np.random.default_rng(seed)
+    n = int(rng.integers(2, 300))
+    m = int(rng.integers(0, 3 * n))
+    src = rng.integers(0, n, m).astype(np.int32)
+    dst = rng.integers(0, n, m).astype(np.int32)
+    g = oracle.build_csr(n, src, dst)
+    a = sp.coo_matrix((np.ones(2 * m), (np.concatenate([src, dst]), np.concatenate([dst, src]))), shape=(n, n)).tocsr()
+    root = int(rng.integers(0, n))
+    ref = shortest_path(a, unweighted=True, indices=root)
+    want = np.where(np.isinf(ref), INT_MAX, ref).astype(np.int64).astype(np.int32)
+    assert np.array_equal(oracle.bfs_serial(g, root), want)
+
+
+@pytest.mark.parametrize("k", [1, 2, 4, 8])
+@pytest.mark.parametrize("seed", range(4))
+def test_kdev_protocol_equals_serial(k, seed):
+    """The reference's multi-device protocol (private distance arrays + owner buckets + min-merge,
+    bfs.cu:569-619, 424-441 / bfs_mpi.cu:581-634) yields the serial depths."""
+    rng = np.random.default_rng(100 + seed)
+    n = 8 * int(rng.integers(1, 40))
+    m = int(rng.integers(1, 4 * n))
+    g = oracle.build_csr(n, rng.integers(0, n, m).astype(np.int32), rng.integers(0, n, m).astype(np.int32))
+    for root in (0, n - 1, int(rng.integers(0, n))):
+        depth, levels = oracle.bfs_kdev(g, root, k)
+        want = oracle.bfs_serial(g, root)
+        assert oracle.check_output(depth, want) == -1
+        assert levels >= int(want[want != INT_MAX].max()) + 1  # re-discovered duplicates may add a level
+
+
+def test_reader_rejects_what_the_reference_mishandles(tmp_path):
+    p = tmp_path / "short.txt"
+    p.write_text("4 3\n0 1\n1 2\n")  # fewer pairs than the header says (bfs.cu:851-861 reads garbage)
+    with pytest.raises(ValueError):
+        oracle.read_edge_file(str(p))
+    p.write_text("4 1\n0 4\n")  # id >= n (bfs.cu:860 indexes out of range)
+    with pytest.raises(ValueError):
+        oracle.read_edge_file(str(p))
+    with pytest.raises(ValueError):
+        oracle.read_edge_file(str(tmp_path / "missing.txt"))
+    p.write_text("3 2\r\n0 1\r\n\r\n1   2\r\n")  # CRLF / blank lines / runs of blanks: `>>` skips all
+    n, s, d = oracle.read_edge_file(str(p))
+    assert (n, s.tolist(), d.tolist()) == (3, [0, 1], [1, 2])
+
+
+def test_generators_shape_and_determinism():
+    for kind in (oracle.GEN_RMAT, oracle.GEN_KRON):
+        n, s, d = oracle.generate_edges(kind, 12, 16, 1)
+        assert n == 4096 and len(s) == 16 * 4096
+        assert s.min() >= 0 and s.max() < n and d.min() >= 0 and d.max() < n
+        _, s2, d2 = oracle.generate_edges(kind, 12, 16, 1, first=1000, count=500)
+        assert np.array_equal(s2, s[1000:1500]) and np.array_equal(d2, d[1000:1500])
+        _, s3, _ = oracle.generate_edges(kind, 12, 16, 2)
+        assert not np.array_equal(s, s3)
+    # RMAT without permutation: vertex 2 is a hub in the giant component
+    n, s, d = oracle.generate_edges(oracle.GEN_RMAT, 16, 16, 1)
+    deg = np.bincount(np.concatenate([s, d]), minlength=n)
+    assert deg[2] > 100
+    # quadrant frequencies ~ (0.57, 0.19, 0.19, 0.05) on the top bit
+    top = ((s >> 15) & 1) * 2 + ((d >> 15) & 1)
+    f = np.bincount(top, minlength=4) / len(s)
+    assert np.allclose(f, [0.57, 0.19, 0.19, 0.05], atol=0.01)
+    # Kronecker = relabelled RMAT: the scramble is a bijection, so the degree multiset is the same
+    nk, sk, dk = oracle.generate_edges(oracle.GEN_KRON, 16, 16, 1)
+    degk = np.bincount(np.concatenate([sk, dk]), minlength=nk)
+    assert np.array_equal(np.sort(deg), np.sort(degk))
+    # grid: 2^5 x 2^5, 4-neighbour, each tuple once
+    n, s, d = oracle.generate_edges(oracle.GEN_GRID, 10, 0, 0)
+    assert n == 1024 and len(s) == 2 * 32 * 31
+    assert set((d - s).tolist()) == {1, 32}
+    g = oracle.build_csr(n, s, d)
+    assert sorted(set(g.sizes.tolist())) == [2, 3, 4]
+    depth = oracle.bfs_serial(g, 0)
+    assert depth.max() == 62  # corner to corner: (32-1)+(32-1)
+
+
+def test_validator_accepts_good_and_rejects_corrupted_trees():
+    n, s, d = oracle.generate_edges(oracle.GEN_RMAT, 9, 8, 5)
+    g = oracle.build_csr(n, s, d)
+    root = 2
+    depth, pe = oracle.bfs_serial(g, root, want_parent=True)
+    # edge index -> vertex id of the discovering endpoint: the row that contains entry i
+    rows = np.repeat(np.arange(n, dtype=np.int32), g.sizes)
+    parent = np.full(n, -1, np.int32)
+    reached = depth != INT_MAX
+    parent[reached] = rows[pe[reached].clip(0, g.adj.size - 1)]
+    parent[root] = root
+    assert oracle.validate_tree(g, root, depth, parent) == (0, -1)
+    bad = parent.copy(); bad[root] = 3
+    assert oracle.validate_tree(g, root, depth, bad)[0] == 1
+    v = int(np.flatnonzero(reached & (depth >= 2))[0])
+    bad = parent.copy(); bad[v] = root if root not in g.adj[g.offsets[v]:g.offsets[v] + g.sizes[v]] else v
+    assert oracle.validate_tree(g, root, depth, bad)[0] in (2, 5)
+    badd = depth.copy(); badd[v] += 1
+    assert oracle.validate_tree(g, root, badd, parent)[0] in (2, 3)
+    iso = int(np.flatnonzero(~reached)[0])
+    bad = parent.copy(); bad[iso] = root
+    assert oracle.validate_tree(g, root, depth, bad)[0] == 4
+    bad = parent.copy(); bad[v] = -1
+    assert oracle.validate_tree(g, root, depth, bad)[0] == 4
+
+
+def test_algorithmic_bytes_formula():
+    path, gold = load_golden("tiny")
+    n, src, dst = oracle.read_edge_file(path)
+    g = oracle.build_csr(n, src, dst)
+    depth = oracle.bfs_serial(g, 2)
+    # reached {0,1,2,3}: D_r = 2+3+2+3 = 10, V_r = 4  ->  4*10 + 8*4 + 8*6
+    assert oracle.reach_stats(g, depth) == (4, 10)
+    assert oracle.algorithmic_bytes(g, depth) == 40 + 32 + 48
