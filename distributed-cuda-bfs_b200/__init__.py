@@ -1,0 +1,237 @@
+"""Python mirror of the C-ABI in include/b2bfs.h (ctypes over lib/libb2bfs.so).
+
+This is plumbing for tests/ and bench.py, not a second implementation: every method is one call
+into the shared library, which in turn runs hand-written sm_100a kernels.  There is no fallback —
+importing works anywhere (so symbol checks can run without a GPU), but creating a handle raises
+unless a CUDA device is present, and a missing library is an ImportError.
+
+The module name has hyphens (it is the directory the task names); import it with
+    importlib.import_module("distributed-cuda-bfs_b200")
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libb2bfs.so")
+CLI_PATH = os.path.join(_HERE, "bin", "b2bfs")
+HEADER_PATH = os.path.abspath(os.path.join(_HERE, "..", "include", "b2bfs.h"))
+
+INT_MAX = 2147483647
+KIND_RMAT, KIND_KRON, KIND_GRID = 0, 1, 2
+MODE_DIRECTION_OPT, MODE_TOP_DOWN = 0, 1
+ENGINE_FUSED, ENGINE_STEPWISE = 0, 1
+
+ERR_NAMES = {0: "OK", -1: "ERR_ARG", -2: "ERR_IO", -3: "ERR_FORMAT", -4: "ERR_RANGE", -5: "ERR_CUDA",
+             -6: "ERR_NOMEM", -7: "ERR_STATE", -8: "ERR_COMM", -9: "ERR_UNSUPPORTED"}
+
+
+class B2BfsError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"{ERR_NAMES.get(code, code)}: {msg}")
+        self.code = code
+
+
+class Stats(C.Structure):
+    _fields_ = [("levels", C.c_int32), ("td_levels", C.c_int32), ("bu_levels", C.c_int32), ("reserved0", C.c_int32),
+                ("reached_vertices", C.c_int64), ("reached_entries", C.c_int64), ("kernel_launches", C.c_int64),
+                ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64), ("search_ms", C.c_double), ("total_ms", C.c_double)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved0"}
+
+
+def build(verbose: bool = False) -> None:
+    """Compile lib/libb2bfs.so and bin/b2bfs for sm_100a (nvcc cross-compiles without a GPU)."""
+    r = subprocess.run(["make", "-C", _HERE, "-j8", "all"], capture_output=True, text=True)
+    if verbose or r.returncode != 0:
+        print(r.stdout[-4000:], r.stderr[-4000:])
+    if r.returncode != 0:
+        raise RuntimeError("libb2bfs build failed")
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: run `make -C {_HERE}` (there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        vp, i64, i32p = C.c_void_p, C.c_int64, C.c_void_p
+        sig = {
+            "b2bfs_version": ([], C.c_char_p),
+            "b2bfs_create": ([C.POINTER(vp), C.c_int], C.c_int),
+            "b2bfs_create_rank": ([C.POINTER(vp), C.c_int, C.c_int, C.c_int, vp], C.c_int),
+            "b2bfs_comm_unique_id": ([vp], C.c_int),
+            "b2bfs_set_option": ([vp, C.c_char_p, i64], C.c_int),
+            "b2bfs_get_option": ([vp, C.c_char_p, C.POINTER(i64)], C.c_int),
+            "b2bfs_load_edge_file": ([vp, C.c_char_p], C.c_int),
+            "b2bfs_load_edges": ([vp, i64, i64, i32p, i32p], C.c_int),
+            "b2bfs_generate": ([vp, C.c_int, C.c_int, C.c_int, C.c_uint64], C.c_int),
+            "b2bfs_num_vertices": ([vp, C.POINTER(i64)], C.c_int),
+            "b2bfs_num_edges": ([vp, C.POINTER(i64)], C.c_int),
+            "b2bfs_num_input_edges": ([vp, C.POINTER(i64)], C.c_int),
+            "b2bfs_csr_entries": ([vp, C.POINTER(i64)], C.c_int),
+            "b2bfs_copy_degrees": ([vp, i32p], C.c_int),
+            "b2bfs_copy_edges": ([vp, i64, i64, i32p, i32p], C.c_int),
+            "b2bfs_copy_csr": ([vp, vp, i32p], C.c_int),
+            "b2bfs_run": ([vp, i64, i32p, i32p, C.POINTER(Stats)], C.c_int),
+            "b2bfs_run_device": ([vp, i64, C.POINTER(Stats)], C.c_int),
+            "b2bfs_device_depth": ([vp, C.POINTER(vp)], C.c_int),
+            "b2bfs_device_parent": ([vp, C.POINTER(vp)], C.c_int),
+            "b2bfs_host_alloc": ([C.POINTER(vp), i64], C.c_int),
+            "b2bfs_host_free": ([vp], C.c_int),
+            "b2bfs_destroy": ([vp], C.c_int),
+            "b2bfs_last_error": ([vp], C.c_char_p),
+        }
+        for name, (args, res) in sig.items():
+            fn = getattr(L, name)
+            fn.argtypes, fn.restype = args, res
+        _lib = L
+    return _lib
+
+
+class PinnedArray:
+    """n x dtype in page-locked host memory (b2bfs_host_alloc), exposed as a numpy view."""
+
+    def __init__(self, n: int, dtype=np.int32):
+        self._p = C.c_void_p()
+        nbytes = int(n) * np.dtype(dtype).itemsize
+        rc = lib().b2bfs_host_alloc(C.byref(self._p), nbytes)
+        if rc:
+            raise B2BfsError(rc, "b2bfs_host_alloc")
+        buf = (C.c_char * max(nbytes, 1)).from_address(self._p.value)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(n))
+
+    @property
+    def ptr(self):
+        return self._p.value
+
+    def free(self):
+        if self._p:
+            self.array = None
+            lib().b2bfs_host_free(self._p)
+            self._p = C.c_void_p()
+
+
+class Bfs:
+    """One handle = one GPU holding one graph.  Mirrors the reference's initCuda2 + runCudaQueueBfs
+    pair (bfs.cu:308, 542): load a graph once, then `run(src)` any number of times."""
+
+    def __init__(self, device: int = 0, **options):
+        self._h = C.c_void_p()
+        rc = lib().b2bfs_create(C.byref(self._h), device)
+        if rc:
+            raise B2BfsError(rc, lib().b2bfs_last_error(None).decode())
+        for k, v in options.items():
+            self.set_option(k, v)
+
+    # -- plumbing
+    def _check(self, rc):
+        if rc:
+            raise B2BfsError(rc, lib().b2bfs_last_error(self._h).decode())
+
+    def close(self):
+        if self._h:
+            lib().b2bfs_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_option(self, key: str, value: int):
+        self._check(lib().b2bfs_set_option(self._h, key.encode(), int(value)))
+
+    def get_option(self, key: str) -> int:
+        v = C.c_int64()
+        self._check(lib().b2bfs_get_option(self._h, key.encode(), C.byref(v)))
+        return v.value
+
+    def _get_i64(self, fn):
+        v = C.c_int64()
+        self._check(fn(self._h, C.byref(v)))
+        return v.value
+
+    # -- graph
+    def load_edge_file(self, path: str):
+        self._check(lib().b2bfs_load_edge_file(self._h, os.fsencode(path)))
+
+    def load_edges(self, n: int, src, dst):
+        src = np.ascontiguousarray(src, np.int32)
+        dst = np.ascontiguousarray(dst, np.int32)
+        assert src.shape == dst.shape
+        self._check(lib().b2bfs_load_edges(self._h, n, src.shape[0], src.ctypes.data, dst.ctypes.data))
+
+    def generate(self, kind: int, scale: int, edgefactor: int = 16, seed: int = 1):
+        self._check(lib().b2bfs_generate(self._h, kind, scale, edgefactor, seed))
+
+    @property
+    def num_vertices(self):
+        return self._get_i64(lib().b2bfs_num_vertices)
+
+    @property
+    def num_edges(self):  # 2m, what the reference prints
+        return self._get_i64(lib().b2bfs_num_edges)
+
+    @property
+    def num_input_edges(self):
+        return self._get_i64(lib().b2bfs_num_input_edges)
+
+    @property
+    def csr_entries(self):
+        return self._get_i64(lib().b2bfs_csr_entries)
+
+    def degrees(self):
+        out = np.empty(self.num_vertices, np.int32)
+        self._check(lib().b2bfs_copy_degrees(self._h, out.ctypes.data))
+        return out
+
+    def edges(self, first: int = 0, count: int | None = None):
+        if count is None:
+            count = self.num_input_edges - first
+        s = np.empty(count, np.int32)
+        d = np.empty(count, np.int32)
+        self._check(lib().b2bfs_copy_edges(self._h, first, count, s.ctypes.data, d.ctypes.data))
+        return s, d
+
+    def csr(self):
+        rowptr = np.empty(self.num_vertices + 1, np.int64)
+        col = np.empty(self.csr_entries, np.int32)
+        self._check(lib().b2bfs_copy_csr(self._h, rowptr.ctypes.data, col.ctypes.data))
+        return rowptr, col
+
+    # -- search
+    def run(self, src: int, want_parent: bool = False, depth_out=None, parent_out=None):
+        """Depths (and parents) into host buffers.  Returns (depth, [parent,] stats dict)."""
+        n = self.num_vertices
+        depth = depth_out if depth_out is not None else np.empty(n, np.int32)
+        parent = parent_out if parent_out is not None else (np.empty(n, np.int32) if want_parent else None)
+        st = Stats()
+        self._check(lib().b2bfs_run(self._h, int(src), depth.ctypes.data,
+                                    parent.ctypes.data if parent is not None else None, C.byref(st)))
+        return (depth, parent, st.as_dict()) if parent is not None else (depth, st.as_dict())
+
+    def run_device(self, src: int):
+        st = Stats()
+        self._check(lib().b2bfs_run_device(self._h, int(src), C.byref(st)))
+        return st.as_dict()
+
+    def device_depth_ptr(self) -> int:
+        p = C.c_void_p()
+        self._check(lib().b2bfs_device_depth(self._h, C.byref(p)))
+        return p.value

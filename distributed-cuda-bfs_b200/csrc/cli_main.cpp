@@ -1,0 +1,163 @@
+// cli_main.cpp — `b2bfs <src_vertex> <edge_file>`: the reference's command line (bfs.cu:783-823,
+// README.md:13) over the C ABI.  Prints the reference's stdout lines (format strings at bfs.cu:830,
+// 846, 848, 876, 789-790, 213, 218, 550, 626, 377-383) so scripts that grep
+// "Elapsed time in milliseconds" / "Output OK!" keep working; exit status 0 on "Output OK!", 1 on
+// a mismatch (bfs.cu:379) or any error.
+//
+// The search result always comes from the GPU.  Like the reference's main (bfs.cu:798-815) the
+// binary then self-checks the depth array against a serial host BFS over the same tuples; that
+// check is verification only (skip it with --no-check) — there is no CPU fallback.
+//
+// Extra, optional flags after the two positionals:
+//   --no-check            skip the host self-check
+//   --dump-depth PATH     write one decimal depth per line (2147483647 = unreachable)
+//   --mode do|td          direction-optimising (default) or top-down only
+//   --engine fused|stepwise
+//   --no-dedup            keep duplicate entries and self-loops in the CSR, as the reference does
+//   --gen KIND:SCALE:EF:SEED   ignore <edge_file>, generate rmat|kron|grid in HBM instead
+//   --device N
+#include <chrono>
+#include <climits>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <queue>
+#include <string>
+#include <vector>
+
+#include "../../include/b2bfs.h"
+
+static int die(b2bfs_t* h, const char* what, int rc) {
+  fprintf(stderr, "b2bfs: %s failed (%d): %s\n", what, rc, b2bfs_last_error(h));
+  if (h) b2bfs_destroy(h);
+  return 1;
+}
+
+// serial host BFS for the self-check: same role as bfsCPU (bfs.cu:923-945), written for this file
+static void host_check_bfs(int64_t n, int64_t m, const std::vector<int32_t>& s, const std::vector<int32_t>& d,
+                           int64_t start, std::vector<int32_t>& depth) {
+  std::vector<int64_t> off(n + 1, 0);
+  for (int64_t i = 0; i < m; ++i) { off[s[i] + 1]++; off[d[i] + 1]++; }
+  for (int64_t v = 0; v < n; ++v) off[v + 1] += off[v];
+  std::vector<int32_t> adj(2 * m);
+  std::vector<int64_t> cur(off.begin(), off.end() - 1);
+  for (int64_t i = 0; i < m; ++i) { adj[cur[s[i]]++] = d[i]; adj[cur[d[i]]++] = s[i]; }
+  depth.assign(n, INT_MAX);
+  std::vector<int32_t> q;
+  q.reserve(n);
+  depth[start] = 0;
+  q.push_back((int32_t)start);
+  for (size_t head = 0; head < q.size(); ++head) {
+    const int32_t u = q[head];
+    for (int64_t i = off[u]; i < off[u + 1]; ++i) {
+      const int32_t v = adj[i];
+      if (depth[v] == INT_MAX) { depth[v] = depth[u] + 1; q.push_back(v); }
+    }
+  }
+}
+
+int main(int argc, char** argv) {
+  if (argc < 3) {
+    fprintf(stderr, "usage: %s <src_vertex> <edge_file> [--no-check] [--dump-depth PATH] [--mode do|td] "
+                    "[--engine fused|stepwise] [--no-dedup] [--gen KIND:SCALE:EF:SEED] [--device N]\n", argv[0]);
+    return 2;
+  }
+  const int64_t start = atoll(argv[1]);  // bfs.cu:786
+  const char* path = argv[2];
+  bool check = true, dedup = true;
+  const char* dump = nullptr;
+  const char* gen = nullptr;
+  int mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED, device = 0;
+  for (int i = 3; i < argc; ++i) {
+    const std::string a(argv[i]);
+    if (a == "--no-check") check = false;
+    else if (a == "--no-dedup") dedup = false;
+    else if (a == "--dump-depth" && i + 1 < argc) dump = argv[++i];
+    else if (a == "--gen" && i + 1 < argc) gen = argv[++i];
+    else if (a == "--device" && i + 1 < argc) device = atoi(argv[++i]);
+    else if (a == "--mode" && i + 1 < argc) mode = strcmp(argv[++i], "td") == 0 ? B2BFS_MODE_TOP_DOWN : B2BFS_MODE_DIRECTION_OPT;
+    else if (a == "--engine" && i + 1 < argc) engine = strcmp(argv[++i], "stepwise") == 0 ? B2BFS_ENGINE_STEPWISE : B2BFS_ENGINE_FUSED;
+    else { fprintf(stderr, "b2bfs: unknown argument %s\n", argv[i]); return 2; }
+  }
+
+  b2bfs_t* h = nullptr;
+  int rc = b2bfs_create(&h, device);
+  if (rc) return die(nullptr, "b2bfs_create", rc);
+  b2bfs_set_option(h, "dedup", dedup);
+  b2bfs_set_option(h, "mode", mode);
+  b2bfs_set_option(h, "engine", engine);
+
+  printf("%s\n", path);  // bfs.cu:830
+  if (gen) {
+    char kind[16] = {0};
+    int scale = 0, ef = 16;
+    unsigned long long seed = 1;
+    if (sscanf(gen, "%15[a-z]:%d:%d:%llu", kind, &scale, &ef, &seed) < 2) { fprintf(stderr, "b2bfs: bad --gen\n"); return 2; }
+    const int k = !strcmp(kind, "kron") ? B2BFS_KIND_KRON : !strcmp(kind, "grid") ? B2BFS_KIND_GRID : B2BFS_KIND_RMAT;
+    rc = b2bfs_generate(h, k, scale, ef, seed);
+    if (rc) return die(h, "b2bfs_generate", rc);
+  } else {
+    rc = b2bfs_load_edge_file(h, path);
+    if (rc) {
+      if (rc == B2BFS_ERR_IO) printf("not open %s\n", path);  // bfs.cu:878
+      return die(h, "b2bfs_load_edge_file", rc);
+    }
+  }
+  int64_t n = 0, m = 0, e2 = 0;
+  b2bfs_num_vertices(h, &n);
+  b2bfs_num_input_edges(h, &m);
+  b2bfs_num_edges(h, &e2);
+  printf("nodes num: %lld\n", (long long)n);  // bfs.cu:846
+  printf("edge num: %lld\n", (long long)m);   // bfs.cu:848
+  printf("finish load graph\n");              // bfs.cu:876
+  printf("Number of vertices %lld\n", (long long)n);    // bfs.cu:789
+  printf("Number of edges %lld\n\n", (long long)e2);    // bfs.cu:790
+  if (start < 0 || start >= n) {
+    fprintf(stderr, "b2bfs: source vertex %lld outside [0, %lld)\n", (long long)start, (long long)n);
+    b2bfs_destroy(h);
+    return 1;
+  }
+
+  std::vector<int32_t> expected;
+  if (check) {
+    std::vector<int32_t> s(m), d(m);
+    rc = b2bfs_copy_edges(h, 0, m, s.data(), d.data());
+    if (rc) return die(h, "b2bfs_copy_edges", rc);
+    printf("Starting sequential bfs.\n");  // bfs.cu:213
+    const auto t0 = std::chrono::steady_clock::now();
+    host_check_bfs(n, m, s, d, start, expected);
+    const long ms = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
+    printf("Elapsed time in milliseconds : %li ms.\n\n", ms);  // bfs.cu:218
+  }
+
+  std::vector<int32_t> depth(n);
+  b2bfs_stats st;
+  printf("Starting queue parallel bfs.\n");  // bfs.cu:550
+  rc = b2bfs_run(h, start, depth.data(), nullptr, &st);
+  if (rc) return die(h, "b2bfs_run", rc);
+  printf("Elapsed time in milliseconds : %li ms.\n", (long)(st.search_ms + 0.5));  // bfs.cu:626
+  fprintf(stderr, "b2bfs: search %.3f ms on device, %d levels (%d top-down, %d bottom-up), %lld vertices reached, "
+                  "%.3f GTEPS\n", st.search_ms, st.levels, st.td_levels, st.bu_levels, (long long)st.reached_vertices,
+          st.search_ms > 0 ? (st.reached_entries / 2) / (st.search_ms * 1e6) : 0.0);
+
+  if (dump) {
+    FILE* f = fopen(dump, "w");
+    if (!f) { fprintf(stderr, "b2bfs: cannot write %s\n", dump); b2bfs_destroy(h); return 1; }
+    for (int64_t i = 0; i < n; ++i) fprintf(f, "%d\n", depth[i]);
+    fclose(f);
+  }
+  int status = 0;
+  if (check) {  // checkOutput, bfs.cu:374-384
+    for (int64_t i = 0; i < n; ++i) {
+      if (depth[i] != expected[i]) {
+        printf("%lld %d %d\n", (long long)i, depth[i], expected[i]);
+        printf("Wrong output!\n");
+        status = 1;
+        break;
+      }
+    }
+    if (!status) printf("Output OK!\n\n");
+  }
+  b2bfs_destroy(h);
+  return status;
+}

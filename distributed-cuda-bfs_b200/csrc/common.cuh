@@ -1,0 +1,143 @@
+// common.cuh — shared declarations of libb2bfs.so (host + device).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdio>
+#include <string>
+
+#include "../../include/b2bfs.h"
+
+namespace b2 {
+
+constexpr int kBlock = 256;              // threads per CTA for every kernel in this library
+constexpr int kWarpsPerBlock = kBlock / 32;
+constexpr int kSMs = 148;                // B200: 2 dies x 74 SMs; grids are sized in multiples of it
+
+// ---------------------------------------------------------------------------------------------
+// error plumbing: every CUDA call is checked (the reference discards all return codes, bfs.cu:336)
+// ---------------------------------------------------------------------------------------------
+struct Status {
+  int code = B2BFS_OK;
+  std::string msg;
+  bool ok() const { return code == B2BFS_OK; }
+};
+
+inline Status make_error(int code, const std::string& msg) {
+  Status s;
+  s.code = code;
+  s.msg = msg;
+  return s;
+}
+
+#define B2_CUDA(expr)                                                                              \
+  do {                                                                                             \
+    cudaError_t _e = (expr);                                                                       \
+    if (_e != cudaSuccess) {                                                                       \
+      return b2::make_error(_e == cudaErrorMemoryAllocation ? B2BFS_ERR_NOMEM : B2BFS_ERR_CUDA,    \
+                            std::string(#expr) + ": " + cudaGetErrorString(_e) + " (" + __FILE__ + \
+                                ":" + std::to_string(__LINE__) + ")");                             \
+    }                                                                                              \
+  } while (0)
+
+#define B2_TRY(expr)           \
+  do {                         \
+    b2::Status _s = (expr);    \
+    if (!_s.ok()) return _s;   \
+  } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// resident graph (this rank's rows) and per-search state, as the kernels see them
+// ---------------------------------------------------------------------------------------------
+struct GraphView {
+  int64_t n;                 // vertices (global)
+  int64_t nwords;            // bitmap words covering n (multiple of 4)
+  int64_t entries;           // resident CSR entries
+  const int64_t* rowptr;     // n+1 offsets into col
+  const int32_t* col;        // neighbour ids, sorted ascending inside a row
+  const uint32_t* visited_init;  // bit set = never scan this vertex bottom-up (degree 0, or id >= n)
+};
+
+// Per-level counters.  Every field that many warps hit with atomics sits on its own 128-byte line
+// (B300_MICROARCH.md "Atomics": distinct lines are ~60x faster than one).
+struct alignas(128) LevelSlot {
+  alignas(128) unsigned int q_count;          // tail of the regular next queue
+  alignas(128) unsigned int hub_count;        // tail of the hub next queue
+  alignas(128) unsigned long long edges;      // sum of degrees of the vertices found this level
+  alignas(128) unsigned long long bu_count;   // vertices found by a bottom-up level
+};
+
+struct SearchResult {
+  int32_t levels, td_levels, bu_levels, pad;
+};
+
+struct Control {
+  LevelSlot slot[4];         // ring indexed by level & 3
+  SearchResult result;
+  int64_t src_degree;        // written by the reset phase (the stepwise host loop starts from it)
+  unsigned long long reached_vertices, reached_entries;  // filled by reach_stats_kernel
+};
+
+struct SearchView {
+  int32_t* depth;            // n
+  int32_t* parent;           // n (vertex ids)
+  uint32_t* visited;         // nwords
+  uint32_t* bitmap[2];       // frontier / next frontier, nwords each; all-zero while top-down runs
+  int32_t* queue[2];         // n each
+  int32_t* hubq[2];          // hub_cap each
+  Control* ctl;
+};
+
+struct Tuning {
+  int mode;                  // B2BFS_MODE_*
+  int alpha;                 // top-down -> bottom-up when m_f > m_u / alpha
+  int beta;                  // bottom-up -> top-down when n_f < n / beta
+  int hub_degree;            // vertices at least this wide go to the hub queue
+};
+
+// Level-loop state; a pure function of the counters, so the host (stepwise engine) and every
+// thread of the persistent kernel (fused engine) compute the same decisions.
+struct LoopState {
+  int level;
+  int mode;                  // 0 top-down, 1 bottom-up
+  int fb;                    // index of the frontier bitmap while bottom-up
+  int done;
+  unsigned int cur_q, cur_hub;
+  unsigned long long prev_nf;
+  unsigned long long unexplored;  // directed entries whose source is still unvisited
+  int td_levels, bu_levels;
+};
+
+enum Conversion { kNoConversion = 0, kQueueToBitmap = 1, kBitmapToQueue = 2 };
+
+__host__ __device__ inline Conversion advance(LoopState& st, const Tuning& tn, int64_t n, unsigned int nq,
+                                              unsigned int nhub, unsigned long long nbu, unsigned long long mf) {
+  const unsigned long long nf = (st.mode == 0) ? (unsigned long long)nq + nhub : nbu;
+  if (st.mode == 0) st.td_levels++; else st.bu_levels++;
+  st.unexplored = (mf > st.unexplored) ? 0ull : st.unexplored - mf;
+  st.level++;
+  Conversion cv = kNoConversion;
+  if (nf == 0) {
+    st.done = 1;
+  } else if (st.mode == 0) {
+    st.cur_q = nq;
+    st.cur_hub = nhub;
+    if (tn.mode == B2BFS_MODE_DIRECTION_OPT && mf > st.unexplored / (unsigned)tn.alpha && nf >= st.prev_nf) {
+      st.mode = 1;
+      st.fb = 0;
+      cv = kQueueToBitmap;
+    }
+  } else {
+    if (nf < (unsigned long long)n / (unsigned)tn.beta && nf < st.prev_nf) {
+      st.mode = 0;
+      cv = kBitmapToQueue;  // cur_q / cur_hub are read back after the conversion
+    } else {
+      st.fb ^= 1;
+    }
+  }
+  st.prev_nf = nf;
+  return cv;
+}
+
+}  // namespace b2

@@ -1,0 +1,325 @@
+// csr_build.cu — edge tuples in HBM -> CSR in HBM, entirely on the GPU.
+//
+// Stands in for the reference's host-side loader tail and flatten loop (bfs.cu:851-875: push v onto
+// u's list and u onto v's, then concatenate rows) and for the H2D half of initCuda2
+// (bfs.cu:333-351).  Instead of n heap vectors on one host core, the 2m directed entries become
+// 64-bit keys (row << vbits | neighbour), are radix-sorted (radix_sort.cu), optionally de-duplicated
+// (duplicates and self-loops never change a BFS depth), and compacted into col[] while the same pass
+// derives rowptr[] from the row boundaries of the sorted keys — no per-vertex atomics.
+//
+// The reference's per-vertex degree (edgesSize, bfs.cu:868 — duplicates and self-loops included) is
+// kept as orig_deg[] because the metric counts input tuples (Graph500 rule), not CSR entries.
+#include "../../include/b2bfs_graphgen.h"
+#include "build.cuh"
+#include "sort.cuh"
+
+namespace b2 {
+
+// ---------------------------------------------------------------------------------------------
+// synthetic edge streams: tuple i is a pure function of (kind, scale, ef, seed, i)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) generate_edges_kernel(int kind, int scale, int ef, uint64_t seed,
+                                                                int64_t first, int64_t count,
+                                                                int32_t* __restrict__ src, int32_t* __restrict__ dst) {
+  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < count; i += (int64_t)gridDim.x * kBlock) {
+    uint32_t u, v;
+    b2_gen_edge(kind, scale, ef, seed, (uint64_t)(first + i), &u, &v);
+    src[i] = (int32_t)u;
+    dst[i] = (int32_t)v;
+  }
+}
+
+Status generate_edges_device(int kind, int scale, int ef, uint64_t seed, int64_t first, int64_t count, int32_t* src,
+                             int32_t* dst, cudaStream_t stream) {
+  if (count <= 0) return Status();
+  const int64_t blocks = (count + kBlock - 1) / kBlock;
+  const int grid = (int)(blocks < (int64_t)kSMs * 16 ? blocks : (int64_t)kSMs * 16);
+  generate_edges_kernel<<<grid, kBlock, 0, stream>>>(kind, scale, ef, seed, first, count, src, dst);
+  B2_CUDA(cudaGetLastError());
+  return Status();
+}
+
+// ---------------------------------------------------------------------------------------------
+// tuples -> keys.  Every tuple (u,v) yields (u -> v) and (v -> u), as bfs.cu:860-861 does; a
+// self-loop yields two identical keys, which keeps orig_deg equal to the reference's edgesSize.
+// Rows outside [row_begin, row_end) are not this rank's: `keys` then receives only owned entries
+// through a warp-aggregated append (cursor != nullptr).  bad_flag is raised for ids outside [0,n).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) expand_edges_kernel(const int32_t* __restrict__ src,
+                                                              const int32_t* __restrict__ dst, int64_t m, int64_t n,
+                                                              int vbits, int64_t row_begin, int64_t row_end,
+                                                              uint64_t* __restrict__ keys,
+                                                              unsigned long long* cursor, int* bad_flag) {
+  const int lane = threadIdx.x & 31;
+  const int64_t stride = (int64_t)gridDim.x * kBlock;
+  const int64_t rounds = (m + stride - 1) / stride;
+  for (int64_t r = 0; r < rounds; ++r) {
+    const int64_t i = r * stride + (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    bool ok = i < m;
+    int64_t u = 0, v = 0;
+    if (ok) {
+      u = src[i];
+      v = dst[i];
+      if (u < 0 || v < 0 || u >= n || v >= n) { *bad_flag = 1; ok = false; }
+    }
+    if (cursor == nullptr) {
+      if (ok) {
+        keys[2 * i] = ((uint64_t)u << vbits) | (uint64_t)v;
+        keys[2 * i + 1] = ((uint64_t)v << vbits) | (uint64_t)u;
+      }
+    } else {
+      const bool a = ok && u >= row_begin && u < row_end;
+      const bool b = ok && v >= row_begin && v < row_end;
+      const unsigned ma = __ballot_sync(0xffffffffu, a), mb = __ballot_sync(0xffffffffu, b);
+      const int na = __popc(ma), nb = __popc(mb);
+      unsigned long long base = 0;
+      if (lane == 0 && na + nb) base = atomicAdd(cursor, (unsigned long long)(na + nb));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      const unsigned lt = (1u << lane) - 1u;
+      if (a) keys[base + __popc(ma & lt)] = ((uint64_t)(u - row_begin) << vbits) | (uint64_t)v;
+      if (b) keys[base + na + __popc(mb & lt)] = ((uint64_t)(v - row_begin) << vbits) | (uint64_t)u;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kBlock) count_owned_kernel(const int32_t* __restrict__ src,
+                                                             const int32_t* __restrict__ dst, int64_t m,
+                                                             int64_t row_begin, int64_t row_end,
+                                                             unsigned long long* total) {
+  unsigned long long c = 0;
+  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < m; i += (int64_t)gridDim.x * kBlock) {
+    const int64_t u = src[i], v = dst[i];
+    c += (u >= row_begin && u < row_end) + (v >= row_begin && v < row_end);
+  }
+  for (int o = 16; o; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(total, c);
+}
+
+// ---------------------------------------------------------------------------------------------
+// sorted keys -> col[] + rowptr[] (+ the undeduplicated row boundaries)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool keep_entry(const uint64_t key, const uint64_t prev, bool first, int dedup, int vbits,
+                                           int64_t row_begin) {
+  if (!dedup) return true;
+  const uint64_t vmask = (1ull << vbits) - 1ull;
+  const int64_t row = (int64_t)(key >> vbits) + row_begin;
+  if ((int64_t)(key & vmask) == row) return false;  // self-loop
+  return first || key != prev;
+}
+
+__global__ void __launch_bounds__(kBlock) count_keep_kernel(const uint64_t* __restrict__ keys, int64_t N,
+                                                            int64_t chunk, int dedup, int vbits, int64_t row_begin,
+                                                            uint64_t* __restrict__ block_counts) {
+  __shared__ unsigned long long total_s;
+  if (threadIdx.x == 0) total_s = 0;
+  __syncthreads();
+  const int64_t begin = (int64_t)blockIdx.x * chunk, end = min(begin + chunk, N);
+  unsigned long long c = 0;
+  for (int64_t i = begin + threadIdx.x; i < end; i += kBlock) {
+    const uint64_t key = keys[i];
+    const uint64_t prev = i > 0 ? keys[i - 1] : 0;
+    c += keep_entry(key, prev, i == 0, dedup, vbits, row_begin);
+  }
+  for (int o = 16; o; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&total_s, c);
+  __syncthreads();
+  if (threadIdx.x == 0) block_counts[blockIdx.x] = total_s;
+}
+
+__global__ void __launch_bounds__(kBlock) compact_kernel(const uint64_t* __restrict__ keys, int64_t N, int64_t chunk,
+                                                         int dedup, int vbits, int64_t row_begin, int64_t nrows,
+                                                         const uint64_t* __restrict__ block_offsets,
+                                                         int32_t* __restrict__ col, int64_t* __restrict__ rowptr,
+                                                         int64_t* __restrict__ orig_rowptr) {
+  __shared__ unsigned int wtot[kWarpsPerBlock];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned lt = (1u << lane) - 1u;
+  const uint64_t vmask = (1ull << vbits) - 1ull;
+  const int64_t begin = (int64_t)blockIdx.x * chunk, end = min(begin + chunk, N);
+  uint64_t carry = block_offsets[blockIdx.x];
+  for (int64_t tile = begin; tile < end; tile += kBlock) {
+    const int64_t i = tile + threadIdx.x;
+    const bool valid = i < end;
+    const uint64_t key = valid ? keys[i] : 0;
+    const uint64_t prev = (valid && i > 0) ? keys[i - 1] : 0;
+    const bool keep = valid && keep_entry(key, prev, i == 0, dedup, vbits, row_begin);
+    const unsigned b = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) wtot[warp] = __popc(b);
+    __syncthreads();
+    unsigned before = 0, total = 0;
+    for (int w = 0; w < kWarpsPerBlock; ++w) {
+      const unsigned c = wtot[w];
+      if (w < warp) before += c;
+      total += c;
+    }
+    const uint64_t P = carry + before + __popc(b & lt);
+    if (keep) col[P] = (int32_t)(key & vmask);
+    if (valid) {
+      const int64_t row = (int64_t)(key >> vbits);
+      const int64_t prow = i > 0 ? (int64_t)(prev >> vbits) : -1;
+      for (int64_t r = prow + 1; r <= row; ++r) {  // rows (prow, row] start here; gaps are empty rows
+        rowptr[r] = (int64_t)P;
+        orig_rowptr[r] = i;
+      }
+      if (i == N - 1) {
+        for (int64_t r = row + 1; r <= nrows; ++r) {
+          rowptr[r] = (int64_t)(P + (keep ? 1 : 0));
+          orig_rowptr[r] = N;
+        }
+      }
+    }
+    carry += total;
+    __syncthreads();
+  }
+}
+
+// orig_deg, the "never scan bottom-up" bitmap (degree-0 rows and the padding past n), hub count
+__global__ void __launch_bounds__(kBlock) finish_rows_kernel(int64_t nrows, int64_t nwords,
+                                                             const int64_t* __restrict__ rowptr,
+                                                             const int64_t* __restrict__ orig_rowptr,
+                                                             uint32_t* __restrict__ orig_deg,
+                                                             uint32_t* __restrict__ visited_init, int hub_degree,
+                                                             unsigned long long* hub_count,
+                                                             unsigned long long* max_degree) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps = (int64_t)gridDim.x * kWarpsPerBlock;
+  unsigned long long mx = 0;
+  for (int64_t w = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5); w < nwords; w += warps) {
+    const int64_t v = w * 32 + lane;
+    bool skip = true, hub = false;
+    if (v < nrows) {
+      const int64_t d = rowptr[v + 1] - rowptr[v];
+      orig_deg[v] = (uint32_t)(orig_rowptr[v + 1] - orig_rowptr[v]);
+      skip = d == 0;
+      hub = d >= hub_degree;
+      mx = d > (int64_t)mx ? (unsigned long long)d : mx;
+    }
+    const unsigned sm = __ballot_sync(0xffffffffu, skip), hm = __ballot_sync(0xffffffffu, hub);
+    if (lane == 0) {
+      visited_init[w] = sm;
+      if (hm) atomicAdd(hub_count, (unsigned long long)__popc(hm));
+    }
+  }
+  for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_down_sync(0xffffffffu, mx, o));
+  if (lane == 0 && mx) atomicMax(max_degree, mx);
+}
+
+static int bits_for(int64_t n) {
+  int b = 1;
+  while (((int64_t)1 << b) < n) ++b;
+  return b;
+}
+
+Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64_t n, int64_t row_begin,
+                        int64_t row_end, bool partitioned, int dedup, int hub_degree, cudaStream_t stream,
+                        BuiltCsr* out, int64_t* launches) {
+  *out = BuiltCsr();
+  const int64_t nrows = row_end - row_begin;
+  const int vbits = bits_for(n);
+  const int rbits = bits_for(nrows > 0 ? nrows : 1);
+  const int64_t nwords = ((nrows + 31) / 32 + 3) / 4 * 4;
+  out->nrows = nrows;
+  out->nwords = nwords;
+
+  unsigned long long* counters = nullptr;  // [0] append cursor / owned total, [1] hub count, [2] max degree
+  int* bad = nullptr;
+  B2_CUDA(cudaMalloc(&counters, 4 * sizeof(unsigned long long)));
+  B2_CUDA(cudaMalloc(&bad, sizeof(int)));
+  B2_CUDA(cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), stream));
+  B2_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), stream));
+
+  const int64_t eblocks = (m + kBlock - 1) / kBlock;
+  const int egrid = (int)(eblocks < (int64_t)kSMs * 16 ? (eblocks > 0 ? eblocks : 1) : (int64_t)kSMs * 16);
+  int64_t N = 2 * m;
+  if (partitioned) {
+    count_owned_kernel<<<egrid, kBlock, 0, stream>>>(src, dst, m, row_begin, row_end, counters);
+    unsigned long long owned = 0;
+    B2_CUDA(cudaMemcpyAsync(&owned, counters, sizeof(owned), cudaMemcpyDeviceToHost, stream));
+    B2_CUDA(cudaStreamSynchronize(stream));
+    B2_CUDA(cudaMemsetAsync(counters, 0, sizeof(unsigned long long), stream));
+    N = (int64_t)owned;
+    if (launches) *launches += 1;
+  }
+
+  uint64_t *ka = nullptr, *kb = nullptr, *sorted = nullptr;
+  void* scratch = nullptr;
+  const size_t kbytes = (size_t)(N > 0 ? N : 1) * sizeof(uint64_t);
+  B2_CUDA(cudaMalloc(&ka, kbytes));
+  B2_CUDA(cudaMalloc(&kb, kbytes));
+  const int G = sort_grid_size(N);
+  B2_CUDA(cudaMalloc(&scratch, sort_scratch_bytes(N) + (size_t)(G + 1) * sizeof(uint64_t)));
+
+  expand_edges_kernel<<<egrid, kBlock, 0, stream>>>(src, dst, m, n, vbits, row_begin, row_end, ka,
+                                                    partitioned ? counters : nullptr, bad);
+  if (launches) *launches += 1;
+  int bad_h = 0;
+  B2_CUDA(cudaMemcpyAsync(&bad_h, bad, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  B2_CUDA(cudaStreamSynchronize(stream));
+  if (bad_h) {
+    cudaFree(ka); cudaFree(kb); cudaFree(scratch); cudaFree(counters); cudaFree(bad);
+    return make_error(B2BFS_ERR_RANGE, "edge list holds a vertex id outside [0, vertex_num)");
+  }
+
+  B2_TRY(radix_sort_u64(ka, kb, N, vbits + rbits, scratch, stream, &sorted, launches));
+
+  // chunked two-pass compaction over the sorted keys
+  int64_t chunk = (N + G - 1) / G;
+  chunk = (chunk + kBlock - 1) / kBlock * kBlock;
+  if (chunk == 0) chunk = kBlock;
+  uint64_t* block_counts = reinterpret_cast<uint64_t*>(scratch);
+  uint64_t* total_d = block_counts + G;
+  count_keep_kernel<<<G, kBlock, 0, stream>>>(sorted, N, chunk, dedup, vbits, row_begin, block_counts);
+  scan_u64_single_block<<<1, 1024, 0, stream>>>(block_counts, G, total_d);
+  uint64_t entries = 0;
+  B2_CUDA(cudaMemcpyAsync(&entries, total_d, sizeof(entries), cudaMemcpyDeviceToHost, stream));
+  B2_CUDA(cudaStreamSynchronize(stream));
+  if (launches) *launches += 2;
+
+  out->entries = (int64_t)entries;
+  out->orig_entries = N;
+  int64_t* orig_rowptr = nullptr;
+  B2_CUDA(cudaMalloc(&out->rowptr, (size_t)(nrows + 1) * sizeof(int64_t)));
+  B2_CUDA(cudaMalloc(&orig_rowptr, (size_t)(nrows + 1) * sizeof(int64_t)));
+  // col is read in 16-byte vectors and 16-byte-aligned bulk copies: pad both ends
+  B2_CUDA(cudaMalloc(&out->col, ((size_t)entries + 64) * sizeof(int32_t)));
+  B2_CUDA(cudaMalloc(&out->orig_deg, (size_t)(nrows > 0 ? nrows : 1) * sizeof(uint32_t)));
+  B2_CUDA(cudaMalloc(&out->visited_init, (size_t)nwords * sizeof(uint32_t)));
+  B2_CUDA(cudaMemsetAsync(out->col + entries, 0xff, 64 * sizeof(int32_t), stream));
+  if (N == 0) {
+    B2_CUDA(cudaMemsetAsync(out->rowptr, 0, (size_t)(nrows + 1) * sizeof(int64_t), stream));
+    B2_CUDA(cudaMemsetAsync(orig_rowptr, 0, (size_t)(nrows + 1) * sizeof(int64_t), stream));
+  } else {
+    compact_kernel<<<G, kBlock, 0, stream>>>(sorted, N, chunk, dedup, vbits, row_begin, nrows, block_counts,
+                                             out->col, out->rowptr, orig_rowptr);
+    if (launches) *launches += 1;
+  }
+  const int64_t fblocks = (nwords + kWarpsPerBlock - 1) / kWarpsPerBlock;
+  const int fgrid = (int)(fblocks < (int64_t)kSMs * 8 ? fblocks : (int64_t)kSMs * 8);
+  finish_rows_kernel<<<fgrid, kBlock, 0, stream>>>(nrows, nwords, out->rowptr, orig_rowptr, out->orig_deg,
+                                                   out->visited_init, hub_degree, counters + 1, counters + 2);
+  if (launches) *launches += 1;
+  unsigned long long hc[2] = {0, 0};
+  B2_CUDA(cudaMemcpyAsync(hc, counters + 1, sizeof(hc), cudaMemcpyDeviceToHost, stream));
+  B2_CUDA(cudaStreamSynchronize(stream));
+  B2_CUDA(cudaGetLastError());
+  out->num_hubs = (int64_t)hc[0];
+  out->max_degree = (int64_t)hc[1];
+
+  cudaFree(orig_rowptr);
+  cudaFree(ka);
+  cudaFree(kb);
+  cudaFree(scratch);
+  cudaFree(counters);
+  cudaFree(bad);
+  return Status();
+}
+
+void free_csr(BuiltCsr* c) {
+  cudaFree(c->rowptr);
+  cudaFree(c->col);
+  cudaFree(c->orig_deg);
+  cudaFree(c->visited_init);
+  *c = BuiltCsr();
+}
+
+}  // namespace b2

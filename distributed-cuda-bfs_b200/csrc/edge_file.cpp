@@ -1,0 +1,172 @@
+// edge_file.cpp — mmap + multi-threaded parse of the reference's edge-list text format.
+//
+// Replaces the front half of readGraphFromFile (bfs.cu:829-863): `f >> n >> m` then m times
+// `f >> u >> v` through std::ifstream on one core.  Same grammar — integers separated by any
+// whitespace, no comments — but the file is mapped once, cut into byte ranges at whitespace, and
+// every range is tokenised by its own thread straight into the (src, dst) arrays.  What the
+// reference leaves undefined is an error here: a file with fewer than 2m integers after the header
+// (bfs.cu:852-861 would push uninitialised values), an id outside [0, n) (bfs.cu:860 indexes out
+// of range) and an unreadable path (bfs.cu:878 only prints "not open").  Tokens past the 2m-th
+// are ignored, as the reference's loop never reads them.
+#include "edge_file.hpp"
+
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <cerrno>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "../../include/b2bfs.h"
+
+namespace b2 {
+
+static inline bool is_space(char c) { return c == ' ' || c == '\n' || c == '\t' || c == '\r' || c == '\v' || c == '\f'; }
+
+int map_file(const char* path, MappedFile* f, std::string* err) {
+  f->fd = open(path, O_RDONLY);
+  if (f->fd < 0) {
+    *err = std::string("not open ") + path + ": " + strerror(errno);
+    return B2BFS_ERR_IO;
+  }
+  struct stat st;
+  if (fstat(f->fd, &st) != 0 || !S_ISREG(st.st_mode)) {
+    *err = std::string("not a regular file: ") + path;
+    close(f->fd);
+    f->fd = -1;
+    return B2BFS_ERR_IO;
+  }
+  f->size = (size_t)st.st_size;
+  if (f->size == 0) {
+    f->data = nullptr;
+    return B2BFS_OK;
+  }
+  void* p = mmap(nullptr, f->size, PROT_READ, MAP_PRIVATE, f->fd, 0);
+  if (p == MAP_FAILED) {
+    *err = std::string("mmap failed: ") + strerror(errno);
+    close(f->fd);
+    f->fd = -1;
+    return B2BFS_ERR_IO;
+  }
+  madvise(p, f->size, MADV_SEQUENTIAL);
+  f->data = static_cast<const char*>(p);
+  return B2BFS_OK;
+}
+
+void unmap_file(MappedFile* f) {
+  if (f->data) munmap(const_cast<char*>(f->data), f->size);
+  if (f->fd >= 0) close(f->fd);
+  *f = MappedFile();
+}
+
+// one non-negative decimal integer starting at p (after optional '+'); false on anything else
+static inline bool parse_uint(const char*& p, const char* end, int64_t* out) {
+  if (p < end && *p == '+') ++p;
+  if (p >= end || *p < '0' || *p > '9') return false;
+  int64_t x = 0;
+  while (p < end && *p >= '0' && *p <= '9') {
+    x = x * 10 + (*p - '0');
+    if (x > ((int64_t)1 << 40)) return false;
+    ++p;
+  }
+  if (p < end && !is_space(*p)) return false;
+  *out = x;
+  return true;
+}
+
+int parse_header(const MappedFile& f, int64_t* n, int64_t* m, size_t* body_off, std::string* err) {
+  const char* p = f.data;
+  const char* end = f.data + f.size;
+  int64_t v[2];
+  for (int k = 0; k < 2; ++k) {
+    while (p < end && is_space(*p)) ++p;
+    if (!parse_uint(p, end, &v[k])) {
+      *err = "edge list header must be two non-negative integers: vertex_num edge_num";
+      return B2BFS_ERR_FORMAT;
+    }
+  }
+  if (v[0] > 0x7fffffffLL) {
+    *err = "vertex_num exceeds int32 ids";
+    return B2BFS_ERR_RANGE;
+  }
+  *n = v[0];
+  *m = v[1];
+  *body_off = (size_t)(p - f.data);
+  return B2BFS_OK;
+}
+
+int parse_body(const MappedFile& f, size_t body_off, int64_t n, int64_t m, int32_t* src, int32_t* dst, int threads,
+               std::string* err) {
+  if (m == 0) return B2BFS_OK;
+  const char* base = f.data;
+  const size_t size = f.size;
+  if (threads < 1) threads = 1;
+  const size_t span = size - body_off;
+  if (span / 64 < (size_t)threads) threads = (int)(span / 64) + 1;
+  // a range owns the tokens that START in it
+  std::vector<size_t> cut(threads + 1);
+  for (int t = 0; t <= threads; ++t) {
+    size_t b = body_off + span * (size_t)t / (size_t)threads;
+    if (t == threads) b = size;
+    else if (t > 0) while (b < size && b > body_off && !is_space(base[b - 1])) ++b;
+    cut[t] = b;
+  }
+  std::vector<int64_t> ntok(threads, 0);
+  std::atomic<int> status(B2BFS_OK);
+  auto count = [&](int t) {
+    const char* p = base + cut[t];
+    const char* e = base + cut[t + 1];
+    int64_t c = 0;
+    while (p < e) {
+      while (p < e && is_space(*p)) ++p;
+      if (p >= e) break;
+      ++c;
+      while (p < base + size && !is_space(*p)) ++p;
+    }
+    ntok[t] = c;
+  };
+  {
+    std::vector<std::thread> th;
+    for (int t = 1; t < threads; ++t) th.emplace_back(count, t);
+    count(0);
+    for (auto& x : th) x.join();
+  }
+  std::vector<int64_t> first(threads + 1, 0);
+  for (int t = 0; t < threads; ++t) first[t + 1] = first[t] + ntok[t];
+  if (first[threads] < 2 * m) {
+    *err = "edge list ends early: header promises " + std::to_string(m) + " pairs, file holds " +
+           std::to_string(first[threads] / 2);
+    return B2BFS_ERR_FORMAT;
+  }
+  auto parse = [&](int t) {
+    const char* p = base + cut[t];
+    const char* e = base + cut[t + 1];
+    const char* fend = base + size;
+    int64_t k = first[t];
+    while (p < e && k < 2 * m) {
+      while (p < e && is_space(*p)) ++p;
+      if (p >= e) break;
+      int64_t x;
+      if (!parse_uint(p, fend, &x)) { status.store(B2BFS_ERR_FORMAT); return; }
+      if (x >= n) { status.store(B2BFS_ERR_RANGE); return; }
+      ((k & 1) ? dst : src)[k >> 1] = (int32_t)x;
+      ++k;
+    }
+  };
+  {
+    std::vector<std::thread> th;
+    for (int t = 1; t < threads; ++t) th.emplace_back(parse, t);
+    parse(0);
+    for (auto& x : th) x.join();
+  }
+  const int rc = status.load();
+  if (rc == B2BFS_ERR_FORMAT) *err = "edge list holds a token that is not a non-negative integer";
+  if (rc == B2BFS_ERR_RANGE) *err = "edge list holds a vertex id >= vertex_num";
+  return rc;
+}
+
+}  // namespace b2

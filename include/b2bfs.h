@@ -1,0 +1,148 @@
+/*
+ * b2bfs.h — C ABI of the B200-native level-synchronous BFS (libb2bfs.so).
+ *
+ * This is the drop-in boundary for the ONE hot path of xxcclong/Distributed-CUDA-BFS
+ * (SURVEY.md §8): edge list -> CSR in HBM -> BFS from a source vertex -> per-vertex int32 depth
+ * (INT_MAX = unreachable).  The reference has no FFI; the seam a maintainer would cut is the pair
+ * initCuda2(Graph&) / runCudaQueueBfs(int, Graph&, vector<int>&, vector<int>&) that its main calls
+ * (bfs.cu:804, 814).  Each entry point below names the reference code it stands in for.  All
+ * citations are into the reference tree (bfs.cu / bfs_mpi.cu).
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 (B2BFS_OK) or a negative
+ * B2BFS_ERR_* code and leaves a message retrievable with b2bfs_last_error().  A handle is not
+ * thread-safe; it owns all device memory, streams and (multi-rank) the NCCL communicator.  Host
+ * output buffers are caller-owned.  There is no CPU fallback: without a CUDA device every compute
+ * call fails with B2BFS_ERR_CUDA.
+ */
+#ifndef B2BFS_H
+#define B2BFS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b2bfs b2bfs_t;
+
+#define B2BFS_OK 0
+#define B2BFS_ERR_ARG -1         /* null pointer, bad option, bad source vertex            */
+#define B2BFS_ERR_IO -2          /* file cannot be opened / mapped                          */
+#define B2BFS_ERR_FORMAT -3      /* malformed edge list (reference: undefined behaviour)   */
+#define B2BFS_ERR_RANGE -4       /* vertex id >= vertex_num (reference: out-of-bounds)     */
+#define B2BFS_ERR_CUDA -5        /* any CUDA runtime failure, incl. "no device"            */
+#define B2BFS_ERR_NOMEM -6
+#define B2BFS_ERR_STATE -7       /* e.g. run before a graph is resident                     */
+#define B2BFS_ERR_COMM -8        /* NCCL failure                                            */
+#define B2BFS_ERR_UNSUPPORTED -9
+
+/* synthetic graph kinds (include/b2bfs_graphgen.h defines the edge streams) */
+#define B2BFS_KIND_RMAT 0
+#define B2BFS_KIND_KRON 1
+#define B2BFS_KIND_GRID 2
+
+/* option "mode" */
+#define B2BFS_MODE_DIRECTION_OPT 0 /* top-down + bottom-up with the switch heuristic (default)     */
+#define B2BFS_MODE_TOP_DOWN 1      /* top-down only: the reference's algorithm (queueBfs)           */
+/* option "engine" */
+#define B2BFS_ENGINE_FUSED 0       /* whole search in ONE persistent cooperative kernel (default)  */
+#define B2BFS_ENGINE_STEPWISE 1    /* one launch per phase, host reads counters per level           */
+
+#define B2BFS_UNREACHED_DEPTH 2147483647 /* INT_MAX, bfs.cu:404, 793 */
+#define B2BFS_UNREACHED_PARENT (-1)
+
+typedef struct b2bfs_stats {
+  int32_t levels;            /* BFS levels executed = eccentricity of the source + 1               */
+  int32_t td_levels;         /* of which top-down                                                   */
+  int32_t bu_levels;         /* of which bottom-up                                                  */
+  int32_t reserved0;
+  int64_t reached_vertices;  /* V_r = #{v : depth[v] != INT_MAX}                                    */
+  int64_t reached_entries;   /* D_r = sum over reached v of the reference's edgesSize[v] = 2*m_r    */
+  int64_t kernel_launches;   /* kernels this call launched                                          */
+  int64_t h2d_bytes;         /* host->device bytes moved by this call                               */
+  int64_t d2h_bytes;         /* device->host bytes moved by this call                               */
+  double search_ms;          /* device time, CUDA events: state reset .. depth complete in HBM     */
+  double total_ms;           /* host wall clock of the whole call incl. copies                      */
+} b2bfs_stats;
+
+/* Library version string. */
+const char* b2bfs_version(void);
+
+/* Create a single-GPU handle on CUDA device `device`.
+ * Replaces the device set-up half of initCuda2 (bfs.cu:308-332: cudaSetDevice, peer enable). */
+int b2bfs_create(b2bfs_t** h, int device);
+
+/* Create one rank of a `world`-rank job (one process per GPU).  `nccl_id` is the 128-byte
+ * ncclUniqueId every rank received from rank 0 (b2bfs_comm_unique_id), over any side channel.
+ * Replaces MPI_Init / MPI_Comm_rank / MPI_Comm_size (bfs_mpi.cu:800-808) and the hard-wired
+ * 2-device layout (`(i+1)%2`, bfs_mpi.cu:576, 615). */
+int b2bfs_create_rank(b2bfs_t** h, int device, int rank, int world, const void* nccl_id);
+int b2bfs_comm_unique_id(void* out128);
+
+/* Options, set before loading a graph unless stated: "dedup" (1: drop duplicate entries and
+ * self-loops while building the CSR — depths do not change; 0: keep the reference's multigraph,
+ * bfs.cu:860-861), "mode", "engine" (both may change between searches), "alpha", "beta" (switch
+ * heuristic), "keep_edges" (1: keep the input tuples resident for b2bfs_copy_edges).
+ * Replaces the reference's compile-time switches (#define DeviceNum, commented call sites in main,
+ * bfs.cu:19, 805-819). */
+int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value);
+int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value);
+
+/* Load a graph: text file in the reference's format ("vertex_num edge_num" then "src dst" lines).
+ * Replaces readGraphFromFile (bfs.cu:829-880) + the H2D half of initCuda2 (bfs.cu:333-351).
+ * Unlike the reference, short files, ids >= vertex_num and unreadable paths are errors. */
+int b2bfs_load_edge_file(b2bfs_t* h, const char* path);
+
+/* Load a graph from host arrays of m (src,dst) tuples over n vertices (0-based ids).
+ * Replaces filling `struct Graph` (bfs.cu:21-27, 851-875) + initCuda2's cudaMalloc/cudaMemcpy. */
+int b2bfs_load_edges(b2bfs_t* h, int64_t n, int64_t m, const int32_t* src, const int32_t* dst);
+
+/* Generate a synthetic graph directly in HBM.  No live reference counterpart (its readGraph random
+ * generator, bfs.cu:882-920, is never called); needed because BASELINE configs 2-5 are too large
+ * for text files. */
+int b2bfs_generate(b2bfs_t* h, int kind, int scale, int edgefactor, uint64_t seed);
+
+/* Graph facts.  num_edges is what the reference prints as "Number of edges" (= 2m directed
+ * entries, bfs.cu:790, 875); num_input_edges is m; csr_entries is what is resident after dedup. */
+int b2bfs_num_vertices(const b2bfs_t* h, int64_t* n);
+int b2bfs_num_edges(const b2bfs_t* h, int64_t* two_m);
+int b2bfs_num_input_edges(const b2bfs_t* h, int64_t* m);
+int b2bfs_csr_entries(const b2bfs_t* h, int64_t* entries);
+
+/* Per-vertex degree in the reference's multigraph = its edgesSize[] (bfs.cu:868), n x int32. */
+int b2bfs_copy_degrees(b2bfs_t* h, int32_t* deg_out);
+/* Input tuples [first, first+count) back to the host (what the loader/generator produced). */
+int b2bfs_copy_edges(b2bfs_t* h, int64_t first, int64_t count, int32_t* src_out, int32_t* dst_out);
+/* Resident CSR back to the host: rowptr has n+1 int64 entries, col has csr_entries int32. */
+int b2bfs_copy_csr(b2bfs_t* h, int64_t* rowptr_out, int32_t* col_out);
+
+/* One search from `src`.  depth_out: n x int32 (INT_MAX = unreachable, depth[src] = 0).
+ * parent_out (nullable): n x int32 VERTEX ids, parent[src] = src, -1 = unreachable (the reference
+ * stores CSR edge indices and never copies them back, bfs.cu:147, 439).  stats nullable.
+ * Replaces runCudaQueueBfs (bfs.cu:542-629; MPI: bfs_mpi.cu:549-643) with its
+ * initializeCudaBfs2 (bfs.cu:402-422) and finalizeCudaBfs (bfs.cu:424-441; bfs_mpi.cu:424-448).
+ * In a multi-rank job every rank calls it with the same src; rank 0's buffers receive all n entries
+ * (other ranks may pass NULL). */
+int b2bfs_run(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent_out, b2bfs_stats* stats);
+
+/* Same search, results left in HBM (no device->host copy). */
+int b2bfs_run_device(b2bfs_t* h, int64_t src, b2bfs_stats* stats);
+/* Device pointers to the last search's results (this rank's rows in a multi-rank job). */
+int b2bfs_device_depth(const b2bfs_t* h, const int32_t** depth_dev);
+int b2bfs_device_parent(const b2bfs_t* h, const int32_t** parent_dev);
+
+/* Page-locked host memory for callers that want the copies in b2bfs_run at full PCIe speed. */
+int b2bfs_host_alloc(void** p, int64_t bytes);
+int b2bfs_host_free(void* p);
+
+/* Release everything the handle owns.  The reference never frees (finalizeCuda is commented out,
+ * bfs.cu:362-372). */
+int b2bfs_destroy(b2bfs_t* h);
+
+/* Message of the last failure on this handle (h may be NULL for create-time failures). */
+const char* b2bfs_last_error(const b2bfs_t* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2BFS_H */
