@@ -15,6 +15,8 @@
 // Every phase is a __device__ function over (blockIdx, gridDim) so both engines run the same code.
 #include <cooperative_groups.h>
 
+#include <cstdlib>
+
 #include "bfs.cuh"
 
 namespace cg = cooperative_groups;
@@ -365,6 +367,7 @@ __device__ void phase_bitmap_to_queue(const BfsParams& p, const LoopState& st) {
   const int64_t nwarps = (int64_t)gridDim.x * kWarpsPerBlock;
   for (int64_t w = gw; w < p.g.nwords; w += nwarps) {
     const uint32_t bits = nx[w];
+    __syncwarp();  // every lane has read the word before lane 0 clears it
     if (lane == 0) { nx[w] = 0; fr[w] = 0; }
     if (!bits) continue;
     const bool set = (bits >> lane) & 1u;
@@ -474,13 +477,20 @@ Status run_stepwise(const BfsParams& p, int64_t src, int grid, cudaStream_t stre
   B2_CUDA(cudaStreamSynchronize(stream));
   LoopState st = initial_state(p, pinned->src_degree);
   int64_t nl = 1;
+  static const bool trace = getenv("B2BFS_TRACE") != nullptr;
   while (!st.done) {
+    if (trace)
+      fprintf(stderr, "[b2bfs] level %d %s frontier q=%u hub=%u unexplored=%llu\n", st.level,
+              st.mode ? "bottom-up" : "top-down", st.cur_q, st.cur_hub, st.unexplored);
     if (st.mode == 0) top_down_kernel<<<grid, kBlock, 0, stream>>>(p, st);
     else bottom_up_kernel<<<grid, kBlock, 0, stream>>>(p, st);
     ++nl;
     B2_CUDA(cudaMemcpyAsync(pinned, p.s.ctl, sizeof(Control), cudaMemcpyDeviceToHost, stream));
     B2_CUDA(cudaStreamSynchronize(stream));
     const LevelSlot& ns = pinned->slot[(st.level + 1) & 3];
+    if (trace)
+      fprintf(stderr, "[b2bfs]   found q=%u hub=%u bu=%llu edges=%llu\n", ns.q_count, ns.hub_count, ns.bu_count,
+              ns.edges);
     const Conversion cv = advance(st, p.tn, p.g.n, ns.q_count, ns.hub_count, ns.bu_count, ns.edges);
     if (cv == kQueueToBitmap) {
       queue_to_bitmap_kernel<<<grid, kBlock, 0, stream>>>(p, st);
