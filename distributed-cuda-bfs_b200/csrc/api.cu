@@ -22,7 +22,7 @@ struct b2bfs {
   std::string err;
   // options
   int dedup = 1, mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED;
-  int alpha = 14, beta = 24, hub_degree = 4096, keep_edges = 1;
+  int alpha = 14, beta = 24, keep_edges = 1;
   // graph
   bool has_graph = false;
   int64_t n = 0, m = 0;
@@ -59,8 +59,8 @@ static void free_search_state(b2bfs* h) {
   cudaFree(h->sv.bitmap[1]);
   cudaFree(h->sv.queue[0]);
   cudaFree(h->sv.queue[1]);
-  cudaFree(h->sv.hubq[0]);
-  cudaFree(h->sv.hubq[1]);
+  cudaFree(h->sv.wideq[0]);
+  cudaFree(h->sv.wideq[1]);
   cudaFree(h->sv.ctl);
   h->sv = SearchView{};
 }
@@ -77,7 +77,7 @@ static void free_graph(b2bfs* h) {
 
 // edges are in d_src/d_dst: build the CSR and the per-search buffers
 static int finish_load(b2bfs* h) {
-  Status s = build_csr_device(h->d_src, h->d_dst, h->m, h->n, 0, h->n, false, h->dedup, h->hub_degree, h->stream,
+  Status s = build_csr_device(h->d_src, h->d_dst, h->m, h->n, 0, h->n, false, h->dedup, h->stream,
                               &h->csr, &h->build_launches);
   if (!s.ok()) {
     free_graph(h);
@@ -89,7 +89,7 @@ static int finish_load(b2bfs* h) {
     h->d_src = h->d_dst = nullptr;
   }
   const int64_t n = h->n, nw = h->csr.nwords;
-  const size_t hub_cap = (size_t)(h->csr.num_hubs > 0 ? h->csr.num_hubs : 1);
+  const size_t wide_cap = (size_t)h->csr.wide_items + 1;
   API_CUDA(h, cudaMalloc(&h->sv.depth, (size_t)(n + 4) * sizeof(int32_t)));
   API_CUDA(h, cudaMalloc(&h->sv.parent, (size_t)(n + 4) * sizeof(int32_t)));
   API_CUDA(h, cudaMalloc(&h->sv.visited, (size_t)nw * sizeof(uint32_t)));
@@ -97,8 +97,8 @@ static int finish_load(b2bfs* h) {
   API_CUDA(h, cudaMalloc(&h->sv.bitmap[1], (size_t)nw * sizeof(uint32_t)));
   API_CUDA(h, cudaMalloc(&h->sv.queue[0], (size_t)n * sizeof(int32_t)));
   API_CUDA(h, cudaMalloc(&h->sv.queue[1], (size_t)n * sizeof(int32_t)));
-  API_CUDA(h, cudaMalloc(&h->sv.hubq[0], hub_cap * sizeof(int32_t)));
-  API_CUDA(h, cudaMalloc(&h->sv.hubq[1], hub_cap * sizeof(int32_t)));
+  API_CUDA(h, cudaMalloc(&h->sv.wideq[0], wide_cap * sizeof(int2)));
+  API_CUDA(h, cudaMalloc(&h->sv.wideq[1], wide_cap * sizeof(int2)));
   API_CUDA(h, cudaMalloc(&h->sv.ctl, sizeof(Control)));
   API_CUDA(h, cudaMemsetAsync(h->sv.ctl, 0, sizeof(Control), h->stream));
   API_CUDA(h, cudaStreamSynchronize(h->stream));
@@ -118,7 +118,6 @@ static BfsParams make_params(const b2bfs* h) {
   p.tn.mode = h->mode;
   p.tn.alpha = h->alpha;
   p.tn.beta = h->beta;
-  p.tn.hub_degree = h->hub_degree;
   return p;
 }
 
@@ -166,7 +165,7 @@ int b2bfs_create_rank(b2bfs_t** out, int device, int rank, int world, const void
 int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
   if (!h || !key) return fail(h, B2BFS_ERR_ARG, "b2bfs_set_option: null argument");
   const std::string k(key);
-  const bool graph_time = (k == "dedup" || k == "hub_degree" || k == "keep_edges");
+  const bool graph_time = (k == "dedup" || k == "keep_edges");
   if (graph_time && h->has_graph) return fail(h, B2BFS_ERR_STATE, "option '" + k + "' must be set before loading a graph");
   if (k == "dedup" && (value == 0 || value == 1)) h->dedup = (int)value;
   else if (k == "keep_edges" && (value == 0 || value == 1)) h->keep_edges = (int)value;
@@ -174,7 +173,6 @@ int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
   else if (k == "engine" && (value == B2BFS_ENGINE_FUSED || value == B2BFS_ENGINE_STEPWISE)) h->engine = (int)value;
   else if (k == "alpha" && value >= 1 && value <= (1 << 20)) h->alpha = (int)value;
   else if (k == "beta" && value >= 1 && value <= (1 << 20)) h->beta = (int)value;
-  else if (k == "hub_degree" && value >= 256 && value <= (1 << 30)) h->hub_degree = (int)value;
   else return fail(h, B2BFS_ERR_ARG, "unknown option or value out of range: " + k);
   return B2BFS_OK;
 }
@@ -188,9 +186,8 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   else if (k == "engine") *value = h->engine;
   else if (k == "alpha") *value = h->alpha;
   else if (k == "beta") *value = h->beta;
-  else if (k == "hub_degree") *value = h->hub_degree;
   else if (k == "grid") *value = h->grid;
-  else if (k == "num_hubs") *value = h->csr.num_hubs;
+  else if (k == "wide_items") *value = h->csr.wide_items;
   else if (k == "max_degree") *value = h->csr.max_degree;
   else if (k == "build_launches") *value = h->build_launches;
   else return B2BFS_ERR_ARG;

@@ -10,7 +10,7 @@
 //   level loop       runCudaQueueBfs, 569-619 (launch + cudaDeviceSynchronize + managed counters
 //                    + cudaMemset per level)
 //
-// Frontier: two int32 queues (regular + hub rows) while top-down, two bitmaps while bottom-up, and
+// Frontier: two work lists (narrow rows + wide-row items) while top-down, two bitmaps while bottom-up, and
 // a visited bitmap that is the claim target (atomicOr) — 2 MiB at scale-24, L2-resident.
 // Every phase is a __device__ function over (blockIdx, gridDim) so both engines run the same code.
 #include <cooperative_groups.h>
@@ -23,9 +23,20 @@ namespace cg = cooperative_groups;
 
 namespace b2 {
 
-constexpr int kWideDegree = 128;   // rows at least this wide are walked by a whole warp, coalesced
-constexpr int kBuProbe = 4;        // neighbours a bottom-up lane checks alone before its warp helps
-constexpr int kHubChunk = 4096;    // entries of a hub row one CTA takes at a time
+constexpr int kBuProbe = 4;          // neighbours a bottom-up lane checks alone before its warp helps
+constexpr int kStageFlush = 160;     // a warp flushes its staging buffer once it holds this many ids
+constexpr int kStageCap = kStageFlush + 128;  // + at most 4 discoveries per lane between two checks
+
+// Per-warp staging of discovered vertices in shared memory: lanes append with shared-memory atomics
+// (no warp-wide vote per edge), and the warp pays ONE global atomic on the queue tail per
+// ~kStageFlush vertices.  A single hot tail counter sustains only ~1 atomic/ns chip-wide
+// (measured: 400 k warp-aggregated appends cost 0.4 ms), so the tail must not be touched per edge.
+struct WarpStage {
+  int32_t narrow[kStageCap];  // rows with degree <  kNarrow
+  int32_t wide[kStageCap];    // rows with degree >= kNarrow ...
+  int32_t witems[kStageCap];  // ... and how many kChunk-entry work items each becomes
+  int ncnt, wcnt;
+};
 
 // ---------------------------------------------------------------------------------------------
 // small helpers
@@ -34,25 +45,6 @@ __device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31; }
 
 __device__ __forceinline__ bool test_bit(const uint32_t* bm, int32_t v) {
   return (bm[(uint32_t)v >> 5] >> (v & 31)) & 1u;
-}
-
-// visited-bitmap claim: cheap read first, atomicOr only when the bit looks clear (a stale "clear"
-// costs one extra atomic, never a wrong answer: bits only ever go 0 -> 1 during a search)
-__device__ __forceinline__ bool claim(uint32_t* visited, int32_t v) {
-  const uint32_t w = (uint32_t)v >> 5, bit = 1u << (v & 31);
-  if (visited[w] & bit) return false;
-  return !(atomicOr(&visited[w], bit) & bit);
-}
-
-// warp-aggregated append of `v` (where flag) to a queue with an atomic tail
-__device__ __forceinline__ void warp_append(bool flag, int32_t v, int32_t* q, unsigned int* tail) {
-  const unsigned m = __ballot_sync(0xffffffffu, flag);
-  if (!m) return;
-  const int leader = __ffs(m) - 1;
-  unsigned base = 0;
-  if ((int)lane_id() == leader) base = atomicAdd(tail, (unsigned)__popc(m));
-  base = __shfl_sync(0xffffffffu, base, leader);
-  if (flag) q[base + __popc(m & ((1u << lane_id()) - 1u))] = v;
 }
 
 // block-level sum of a 64-bit per-thread value -> one atomic per CTA
@@ -67,6 +59,54 @@ __device__ __forceinline__ void block_accumulate(unsigned long long x, unsigned 
     if (t) atomicAdd(target, t);
   }
   __syncthreads();
+}
+
+// Route a newly discovered vertex of degree d to the next level's work lists (lane-local).
+__device__ __forceinline__ void route_vertex(WarpStage& sg, int32_t v, int64_t d) {
+  if (d < kNarrow) {
+    sg.narrow[atomicAdd(&sg.ncnt, 1)] = v;
+  } else {
+    const int pos = atomicAdd(&sg.wcnt, 1);
+    sg.wide[pos] = v;
+    sg.witems[pos] = (int32_t)((d + kChunk - 1) / kChunk);
+  }
+}
+
+// Warp-uniform: drain the staging buffers into the global queues when they are full enough.
+__device__ __forceinline__ void stage_flush(WarpStage& sg, LevelSlot* ns, int32_t* nq, int2* nwq, bool force) {
+  __syncwarp();
+  const unsigned lane = lane_id();
+  const int nc = *reinterpret_cast<volatile int*>(&sg.ncnt);
+  const int wc = *reinterpret_cast<volatile int*>(&sg.wcnt);
+  if (nc >= kStageFlush || (force && nc > 0)) {
+    unsigned base = 0;
+    if (lane == 0) base = atomicAdd(&ns->q_count, (unsigned)nc);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    for (int i = lane; i < nc; i += 32) nq[base + i] = sg.narrow[i];
+    __syncwarp();
+    if (lane == 0) sg.ncnt = 0;
+  }
+  if (wc >= kStageFlush || (force && wc > 0)) {
+    for (int i0 = 0; i0 < wc; i0 += 32) {  // one tail atomic per 32 staged rows
+      const int i = i0 + (int)lane;
+      const unsigned items = i < wc ? (unsigned)sg.witems[i] : 0u;
+      unsigned incl = items;
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= (unsigned)o) incl += y;
+      }
+      unsigned base = 0;
+      if (lane == 31) base = atomicAdd(&ns->wide_count, incl);
+      base = __shfl_sync(0xffffffffu, base, 31) + incl - items;
+      if (items) {
+        const int32_t v = sg.wide[i];
+        for (unsigned c = 0; c < items; ++c) nwq[base + c] = make_int2(v, (int)c);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) sg.wcnt = 0;
+  }
+  __syncwarp();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -119,17 +159,18 @@ __device__ void phase_init(const BfsParams& p, int64_t src) {
     Control* c = p.s.ctl;
     for (int k = 0; k < 4; ++k) {
       c->slot[k].q_count = 0;
-      c->slot[k].hub_count = 0;
+      c->slot[k].wide_count = 0;
       c->slot[k].edges = 0;
       c->slot[k].bu_count = 0;
     }
     const int64_t deg = p.g.rowptr[src + 1] - p.g.rowptr[src];
-    if (deg >= p.tn.hub_degree) {
-      p.s.hubq[0][0] = (int32_t)src;
-      c->slot[0].hub_count = 1;
-    } else {
+    if (deg < kNarrow) {
       p.s.queue[0][0] = (int32_t)src;
       c->slot[0].q_count = 1;
+    } else {
+      const unsigned items = (unsigned)((deg + kChunk - 1) / kChunk);
+      for (unsigned k = 0; k < items; ++k) p.s.wideq[0][k] = make_int2((int)src, (int)k);
+      c->slot[0].wide_count = items;
     }
     c->result.levels = c->result.td_levels = c->result.bu_levels = 0;
     c->src_degree = deg;
@@ -142,9 +183,9 @@ __host__ __device__ inline LoopState initial_state(const BfsParams& p, int64_t s
   st.mode = 0;
   st.fb = 0;
   st.done = 0;
-  const bool hub = src_degree >= p.tn.hub_degree;
-  st.cur_q = hub ? 0u : 1u;
-  st.cur_hub = hub ? 1u : 0u;
+  const bool wide = src_degree >= kNarrow;
+  st.cur_q = wide ? 0u : 1u;
+  st.cur_wide = wide ? (unsigned)((src_degree + kChunk - 1) / kChunk) : 0u;
   st.prev_nf = 1;
   st.unexplored = (unsigned long long)(p.g.entries - src_degree);
   st.td_levels = st.bu_levels = 0;
@@ -152,112 +193,104 @@ __host__ __device__ inline LoopState initial_state(const BfsParams& p, int64_t s
 }
 
 // ---------------------------------------------------------------------------------------------
-// top-down: one warp-wide visit of up to 32 (u -> v) entries
+// top-down.  Work items, strided over ALL warps of the grid so that a frontier of a few heavy rows
+// (the neighbours of any root in a power-law graph) still spreads over the whole chip:
+//   narrow tile  32 frontier rows of degree < kNarrow: warp scan over the degrees, then 32 entries
+//                per step regardless of row boundaries
+//   wide item    <= kChunk consecutive entries of one row: 16-byte vector loads, 128 entries per step
+// Each lane then works alone: probe the visited bitmap, atomicOr to claim, write depth/parent, read
+// the new vertex's degree and stage it for the next level.
+// algorithmic bytes per level: 4 B per frontier vertex / 8 B per item + 16 B row extent + 4 B per
+// neighbour entry; per discovered vertex 8 B (depth + parent) + 16 B its row extent + 4-8 B queue
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void td_visit(const BfsParams& p, int level, LevelSlot* ns, int32_t* nq, int32_t* nhq,
-                                         bool active, int32_t v, int32_t u, unsigned long long& edges_acc) {
-  const bool win = active && claim(p.s.visited, v);
-  int64_t deg = 0;
-  if (win) {
-    p.s.depth[v] = level + 1;
-    p.s.parent[v] = u;
-    deg = __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v);
-    edges_acc += (unsigned long long)deg;
-  }
-  const bool hub = win && deg >= p.tn.hub_degree;
-  warp_append(win && !hub, v, nq, &ns->q_count);
-  warp_append(hub, v, nhq, &ns->hub_count);
+__device__ __forceinline__ void td_visit(const BfsParams& p, int level, WarpStage& sg, int32_t v, int32_t u,
+                                         unsigned long long& edges_acc) {
+  const uint32_t w = (uint32_t)v >> 5, bit = 1u << (v & 31);
+  // cheap read first; a stale "clear" only costs one extra atomic (bits only go 0 -> 1 in a search)
+  if (p.s.visited[w] & bit) return;
+  if (atomicOr(&p.s.visited[w], bit) & bit) return;
+  p.s.depth[v] = level + 1;
+  p.s.parent[v] = u;
+  const int64_t d = __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v);
+  edges_acc += (unsigned long long)d;
+  route_vertex(sg, v, d);
 }
 
-// algorithmic bytes per level: 4 B per frontier vertex (queue) + 16 B row extent + 4 B per
-// neighbour entry; per discovered vertex 8 B (depth + parent) + 4 B queue + 16 B its row extent
-__device__ void phase_top_down(const BfsParams& p, const LoopState& st) {
+__device__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStage* stage) {
   const int level = st.level;
   const int32_t* q = p.s.queue[level & 1];
-  const int32_t* hq = p.s.hubq[level & 1];
+  const int2* wq = p.s.wideq[level & 1];
   int32_t* nq = p.s.queue[(level + 1) & 1];
-  int32_t* nhq = p.s.hubq[(level + 1) & 1];
+  int2* nwq = p.s.wideq[(level + 1) & 1];
   LevelSlot* ns = &p.s.ctl->slot[(level + 1) & 3];
   const unsigned lane = lane_id();
+  WarpStage& sg = stage[threadIdx.x >> 5];
   const int64_t gw = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)gridDim.x * kWarpsPerBlock;
   unsigned long long edges_acc = 0;
 
+  if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
   if (blockIdx.x == 0 && threadIdx.x == 0) {  // recycle the slot two levels ahead
     LevelSlot* z = &p.s.ctl->slot[(level + 2) & 3];
-    z->q_count = 0; z->hub_count = 0; z->edges = 0; z->bu_count = 0;
+    z->q_count = 0; z->wide_count = 0; z->edges = 0; z->bu_count = 0;
   }
+  __syncwarp();
 
-  // regular rows: 32 frontier vertices per warp tile
-  for (int64_t tile = gw; tile * 32 < (int64_t)st.cur_q; tile += nwarps) {
-    const int64_t idx = tile * 32 + lane;
-    const bool has = idx < (int64_t)st.cur_q;
-    const int32_t u = has ? q[idx] : 0;
-    int64_t rs = 0, re = 0;
-    if (has) {
-      rs = __ldg(p.g.rowptr + u);
-      re = __ldg(p.g.rowptr + u + 1);
-    }
-    const uint32_t deg = (uint32_t)(re - rs);
-    // wide rows: the whole warp walks one row, 128 contiguous bytes per step
-    unsigned wide = __ballot_sync(0xffffffffu, deg >= (uint32_t)kWideDegree);
-    while (wide) {
-      const int l = __ffs(wide) - 1;
-      wide &= wide - 1;
-      const int64_t ss = __shfl_sync(0xffffffffu, rs, l), ee = __shfl_sync(0xffffffffu, re, l);
-      const int32_t uu = __shfl_sync(0xffffffffu, u, l);
-      for (int64_t base = ss; base < ee; base += 32) {
-        const int64_t i = base + lane;
-        const bool a = i < ee;
-        const int32_t v = a ? __ldg(p.g.col + i) : 0;
-        td_visit(p, level, ns, nq, nhq, a, v, uu, edges_acc);
+  const int64_t tiles = ((int64_t)st.cur_q + 31) >> 5;
+  const int64_t work = tiles + (int64_t)st.cur_wide;
+  for (int64_t item = gw; item < work; item += nwarps) {
+    if (item < tiles) {
+      const int64_t idx = item * 32 + lane;
+      const bool has = idx < (int64_t)st.cur_q;
+      const int32_t u = has ? q[idx] : 0;
+      int64_t rs = 0;
+      uint32_t d = 0;
+      if (has) {
+        rs = __ldg(p.g.rowptr + u);
+        d = (uint32_t)(__ldg(p.g.rowptr + u + 1) - rs);
       }
-    }
-    // narrow rows: warp scan over degrees, then 32 entries per step regardless of row boundaries
-    const uint32_t d = deg >= (uint32_t)kWideDegree ? 0u : deg;
-    uint32_t incl = d;
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= (unsigned)o) incl += y;
-    }
-    const uint32_t excl = incl - d;
-    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-    for (uint32_t base = 0; base < total; base += 32) {
-      const uint32_t k = base + lane;
-      const bool a = k < total;
-      int lo = 0, hi = 31;  // owner = largest lane whose exclusive prefix is <= k
+      uint32_t incl = d;
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= (unsigned)o) incl += y;
+      }
+      const uint32_t excl = incl - d;
+      const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+      for (uint32_t base = 0; base < total; base += 32) {
+        const uint32_t k = base + lane;
+        int lo = 0, hi = 31;  // owner = largest lane whose exclusive prefix is <= k
 #pragma unroll
-      for (int s = 0; s < 5; ++s) {
-        const int mid = (lo + hi + 1) >> 1;
-        const uint32_t val = __shfl_sync(0xffffffffu, excl, mid);
-        if (val <= k) lo = mid; else hi = mid - 1;
+        for (int s = 0; s < 5; ++s) {
+          const int mid = (lo + hi + 1) >> 1;
+          const uint32_t val = __shfl_sync(0xffffffffu, excl, mid);
+          if (val <= k) lo = mid; else hi = mid - 1;
+        }
+        const uint32_t oe = __shfl_sync(0xffffffffu, excl, lo);
+        const int64_t ors = __shfl_sync(0xffffffffu, rs, lo);
+        const int32_t uu = __shfl_sync(0xffffffffu, u, lo);
+        if (k < total) td_visit(p, level, sg, __ldg(p.g.col + ors + (k - oe)), uu, edges_acc);
+        stage_flush(sg, ns, nq, nwq, false);
       }
-      const uint32_t oe = __shfl_sync(0xffffffffu, excl, lo);
-      const int64_t ors = __shfl_sync(0xffffffffu, rs, lo);
-      const int32_t uu = __shfl_sync(0xffffffffu, u, lo);
-      const int32_t v = a ? __ldg(p.g.col + ors + (k - oe)) : 0;
-      td_visit(p, level, ns, nq, nhq, a, v, uu, edges_acc);
+    } else {
+      const int2 it = wq[item - tiles];
+      const int32_t u = it.x;
+      const int64_t rs = __ldg(p.g.rowptr + u) + (int64_t)it.y * kChunk;
+      const int64_t re = min(__ldg(p.g.rowptr + u + 1), rs + kChunk);
+      // col is 16-byte aligned at index 0 and padded past its end: align the window down to 4 entries
+      for (int64_t b0 = rs & ~(int64_t)3; b0 < re; b0 += 128) {  // warp-uniform trip count
+        const int64_t base = b0 + 4 * lane;
+        if (base < re) {
+          const int4 x = __ldg(reinterpret_cast<const int4*>(p.g.col + base));
+          if (base >= rs) td_visit(p, level, sg, x.x, u, edges_acc);
+          if (base + 1 >= rs && base + 1 < re) td_visit(p, level, sg, x.y, u, edges_acc);
+          if (base + 2 >= rs && base + 2 < re) td_visit(p, level, sg, x.z, u, edges_acc);
+          if (base + 3 >= rs && base + 3 < re) td_visit(p, level, sg, x.w, u, edges_acc);
+        }
+        stage_flush(sg, ns, nq, nwq, false);
+      }
     }
   }
-
-  // hub rows: every CTA takes kHubChunk-entry slices of each hub, rotated so hubs start on
-  // different CTAs
-  for (unsigned h = 0; h < st.cur_hub; ++h) {
-    const int32_t u = hq[h];
-    const int64_t rs = __ldg(p.g.rowptr + u), re = __ldg(p.g.rowptr + u + 1);
-    const int64_t chunks = (re - rs + kHubChunk - 1) / kHubChunk;
-    const int64_t first = ((int64_t)blockIdx.x + gridDim.x - (int64_t)((h * 37u) % gridDim.x)) % gridDim.x;
-    for (int64_t c = first; c < chunks; c += gridDim.x) {
-      const int64_t cs = rs + c * kHubChunk;
-      const int64_t ce = min(cs + kHubChunk, re);
-      for (int64_t base = cs + (threadIdx.x & ~31); base < ce; base += kBlock) {
-        const int64_t i = base + lane;
-        const bool a = i < ce;
-        const int32_t v = a ? __ldg(p.g.col + i) : 0;
-        td_visit(p, level, ns, nq, nhq, a, v, u, edges_acc);
-      }
-    }
-  }
+  stage_flush(sg, ns, nq, nwq, true);
   block_accumulate(edges_acc, &ns->edges);
 }
 
@@ -282,7 +315,7 @@ __device__ void phase_bottom_up(const BfsParams& p, const LoopState& st) {
 
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     LevelSlot* z = &p.s.ctl->slot[(level + 2) & 3];
-    z->q_count = 0; z->hub_count = 0; z->edges = 0; z->bu_count = 0;
+    z->q_count = 0; z->wide_count = 0; z->edges = 0; z->bu_count = 0;
   }
 
   for (int64_t w = gw; w < p.g.nwords; w += nwarps) {
@@ -338,59 +371,70 @@ __device__ void phase_bottom_up(const BfsParams& p, const LoopState& st) {
 // ---------------------------------------------------------------------------------------------
 // representation changes at a direction switch
 // ---------------------------------------------------------------------------------------------
-// queues of the new frontier (level st.level) -> bitmap[0]; both bitmaps are all-zero on entry
+// work lists of the new frontier (level st.level) -> bitmap[0]; both bitmaps are all-zero on entry
 __device__ void phase_queue_to_bitmap(const BfsParams& p, const LoopState& st) {
   const int32_t* q = p.s.queue[st.level & 1];
-  const int32_t* hq = p.s.hubq[st.level & 1];
+  const int2* wq = p.s.wideq[st.level & 1];
   uint32_t* bm = p.s.bitmap[0];
   const int64_t tid = (int64_t)blockIdx.x * kBlock + threadIdx.x, nthreads = (int64_t)gridDim.x * kBlock;
   for (int64_t i = tid; i < (int64_t)st.cur_q; i += nthreads) {
     const int32_t v = q[i];
     atomicOr(&bm[(uint32_t)v >> 5], 1u << (v & 31));
   }
-  for (int64_t i = tid; i < (int64_t)st.cur_hub; i += nthreads) {
-    const int32_t v = hq[i];
-    atomicOr(&bm[(uint32_t)v >> 5], 1u << (v & 31));
+  for (int64_t i = tid; i < (int64_t)st.cur_wide; i += nthreads) {
+    const int2 it = wq[i];
+    if (it.y == 0) atomicOr(&bm[(uint32_t)it.x >> 5], 1u << (it.x & 31));
   }
 }
 
-// next bitmap (written by the bottom-up level that just ended) -> queues of level st.level, routed
-// by degree; clears both bitmaps so the "all-zero while top-down" invariant holds again
-__device__ void phase_bitmap_to_queue(const BfsParams& p, const LoopState& st) {
+// next bitmap (written by the bottom-up level that just ended) -> work lists of level st.level,
+// routed by degree through the same per-warp staging; clears both bitmaps so the "all-zero while
+// top-down" invariant holds again
+__device__ void phase_bitmap_to_queue(const BfsParams& p, const LoopState& st, WarpStage* stage) {
   uint32_t* nx = p.s.bitmap[st.fb ^ 1];
   uint32_t* fr = p.s.bitmap[st.fb];
   int32_t* q = p.s.queue[st.level & 1];
-  int32_t* hq = p.s.hubq[st.level & 1];
+  int2* wq = p.s.wideq[st.level & 1];
   LevelSlot* cs = &p.s.ctl->slot[st.level & 3];
   const unsigned lane = lane_id();
+  WarpStage& sg = stage[threadIdx.x >> 5];
+  if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
+  __syncwarp();
   const int64_t gw = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)gridDim.x * kWarpsPerBlock;
   for (int64_t w = gw; w < p.g.nwords; w += nwarps) {
-    const uint32_t bits = nx[w];
-    __syncwarp();  // every lane has read the word before lane 0 clears it
-    if (lane == 0) { nx[w] = 0; fr[w] = 0; }
+    uint32_t bits = 0;
+    if (lane == 0) {
+      bits = nx[w];
+      nx[w] = 0;
+      fr[w] = 0;
+    }
+    bits = __shfl_sync(0xffffffffu, bits, 0);
     if (!bits) continue;
-    const bool set = (bits >> lane) & 1u;
-    const int64_t v = w * 32 + lane;
-    int64_t deg = 0;
-    if (set) deg = __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v);
-    const bool hub = set && deg >= p.tn.hub_degree;
-    warp_append(set && !hub, (int32_t)v, q, &cs->q_count);
-    warp_append(hub, (int32_t)v, hq, &cs->hub_count);
+    if ((bits >> lane) & 1u) {
+      const int64_t v = w * 32 + lane;
+      route_vertex(sg, (int32_t)v, __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v));
+    }
+    stage_flush(sg, cs, q, wq, false);
   }
+  stage_flush(sg, cs, q, wq, true);
 }
 
 // ---------------------------------------------------------------------------------------------
 // stepwise engine: one kernel per phase
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock) search_init_kernel(BfsParams p, int64_t src) { phase_init(p, src); }
-__global__ void __launch_bounds__(kBlock) top_down_kernel(BfsParams p, LoopState st) { phase_top_down(p, st); }
+__global__ void __launch_bounds__(kBlock) top_down_kernel(BfsParams p, LoopState st) {
+  __shared__ WarpStage stage[kWarpsPerBlock];
+  phase_top_down(p, st, stage);
+}
 __global__ void __launch_bounds__(kBlock) bottom_up_kernel(BfsParams p, LoopState st) { phase_bottom_up(p, st); }
 __global__ void __launch_bounds__(kBlock) queue_to_bitmap_kernel(BfsParams p, LoopState st) {
   phase_queue_to_bitmap(p, st);
 }
 __global__ void __launch_bounds__(kBlock) bitmap_to_queue_kernel(BfsParams p, LoopState st) {
-  phase_bitmap_to_queue(p, st);
+  __shared__ WarpStage stage[kWarpsPerBlock];
+  phase_bitmap_to_queue(p, st, stage);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -407,25 +451,26 @@ __device__ __forceinline__ unsigned long long ld_volatile(const unsigned long lo
 }
 
 __global__ void __launch_bounds__(kBlock) bfs_fused_kernel(BfsParams p, int64_t src) {
+  __shared__ WarpStage stage[kWarpsPerBlock];
   cg::grid_group grid = cg::this_grid();
   phase_init(p, src);
   LoopState st = initial_state(p, __ldg(p.g.rowptr + src + 1) - __ldg(p.g.rowptr + src));
   grid.sync();
   while (!st.done) {
-    if (st.mode == 0) phase_top_down(p, st); else phase_bottom_up(p, st);
+    if (st.mode == 0) phase_top_down(p, st, stage); else phase_bottom_up(p, st);
     grid.sync();
     const LevelSlot* ns = &p.s.ctl->slot[(st.level + 1) & 3];
-    const Conversion cv = advance(st, p.tn, p.g.n, ld_volatile(&ns->q_count), ld_volatile(&ns->hub_count),
+    const Conversion cv = advance(st, p.tn, p.g.n, ld_volatile(&ns->q_count), ld_volatile(&ns->wide_count),
                                   ld_volatile(&ns->bu_count), ld_volatile(&ns->edges));
     if (cv == kQueueToBitmap) {
       phase_queue_to_bitmap(p, st);
       grid.sync();
     } else if (cv == kBitmapToQueue) {
-      phase_bitmap_to_queue(p, st);
+      phase_bitmap_to_queue(p, st, stage);
       grid.sync();
       const LevelSlot* cs = &p.s.ctl->slot[st.level & 3];
       st.cur_q = ld_volatile(&cs->q_count);
-      st.cur_hub = ld_volatile(&cs->hub_count);
+      st.cur_wide = ld_volatile(&cs->wide_count);
     }
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -480,8 +525,8 @@ Status run_stepwise(const BfsParams& p, int64_t src, int grid, cudaStream_t stre
   static const bool trace = getenv("B2BFS_TRACE") != nullptr;
   while (!st.done) {
     if (trace)
-      fprintf(stderr, "[b2bfs] level %d %s frontier q=%u hub=%u unexplored=%llu\n", st.level,
-              st.mode ? "bottom-up" : "top-down", st.cur_q, st.cur_hub, st.unexplored);
+      fprintf(stderr, "[b2bfs] level %d %s frontier q=%u wide=%u unexplored=%llu\n", st.level,
+              st.mode ? "bottom-up" : "top-down", st.cur_q, st.cur_wide, st.unexplored);
     if (st.mode == 0) top_down_kernel<<<grid, kBlock, 0, stream>>>(p, st);
     else bottom_up_kernel<<<grid, kBlock, 0, stream>>>(p, st);
     ++nl;
@@ -489,9 +534,9 @@ Status run_stepwise(const BfsParams& p, int64_t src, int grid, cudaStream_t stre
     B2_CUDA(cudaStreamSynchronize(stream));
     const LevelSlot& ns = pinned->slot[(st.level + 1) & 3];
     if (trace)
-      fprintf(stderr, "[b2bfs]   found q=%u hub=%u bu=%llu edges=%llu\n", ns.q_count, ns.hub_count, ns.bu_count,
+      fprintf(stderr, "[b2bfs]   found q=%u wide=%u bu=%llu edges=%llu\n", ns.q_count, ns.wide_count, ns.bu_count,
               ns.edges);
-    const Conversion cv = advance(st, p.tn, p.g.n, ns.q_count, ns.hub_count, ns.bu_count, ns.edges);
+    const Conversion cv = advance(st, p.tn, p.g.n, ns.q_count, ns.wide_count, ns.bu_count, ns.edges);
     if (cv == kQueueToBitmap) {
       queue_to_bitmap_kernel<<<grid, kBlock, 0, stream>>>(p, st);
       ++nl;
@@ -501,7 +546,7 @@ Status run_stepwise(const BfsParams& p, int64_t src, int grid, cudaStream_t stre
       B2_CUDA(cudaMemcpyAsync(pinned, p.s.ctl, sizeof(Control), cudaMemcpyDeviceToHost, stream));
       B2_CUDA(cudaStreamSynchronize(stream));
       st.cur_q = pinned->slot[st.level & 3].q_count;
-      st.cur_hub = pinned->slot[st.level & 3].hub_count;
+      st.cur_wide = pinned->slot[st.level & 3].wide_count;
     }
   }
   B2_CUDA(cudaGetLastError());

@@ -9,7 +9,7 @@ struct BuiltCsr {
   int64_t nwords = 0;        // bitmap words covering nrows (multiple of 4)
   int64_t entries = 0;       // resident col entries (after dedup)
   int64_t orig_entries = 0;  // directed entries before dedup (= the reference's numEdges for these rows)
-  int64_t num_hubs = 0;      // rows with degree >= hub_degree
+  int64_t wide_items = 0;    // sum over rows with degree >= kNarrow of ceil(degree / kChunk)
   int64_t max_degree = 0;
   int64_t* rowptr = nullptr;        // nrows + 1
   int32_t* col = nullptr;           // entries (+64 padding ints)
@@ -21,7 +21,7 @@ Status generate_edges_device(int kind, int scale, int ef, uint64_t seed, int64_t
                              int32_t* dst, cudaStream_t stream);
 
 Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64_t n, int64_t row_begin,
-                        int64_t row_end, bool partitioned, int dedup, int hub_degree, cudaStream_t stream,
+                        int64_t row_end, bool partitioned, int dedup, cudaStream_t stream,
                         BuiltCsr* out, int64_t* launches);
 
 void free_csr(BuiltCsr* c);

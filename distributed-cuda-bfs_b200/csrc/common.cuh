@@ -14,6 +14,8 @@ namespace b2 {
 constexpr int kBlock = 256;              // threads per CTA for every kernel in this library
 constexpr int kWarpsPerBlock = kBlock / 32;
 constexpr int kSMs = 148;                // B200: 2 dies x 74 SMs; grids are sized in multiples of it
+constexpr int kNarrow = 32;              // rows narrower than this are gathered 32 at a time by one warp
+constexpr int kChunk = 256;              // wider rows are cut into work items of this many entries
 
 // ---------------------------------------------------------------------------------------------
 // error plumbing: every CUDA call is checked (the reference discards all return codes, bfs.cu:336)
@@ -63,7 +65,7 @@ struct GraphView {
 // (B300_MICROARCH.md "Atomics": distinct lines are ~60x faster than one).
 struct alignas(128) LevelSlot {
   alignas(128) unsigned int q_count;          // tail of the regular next queue
-  alignas(128) unsigned int hub_count;        // tail of the hub next queue
+  alignas(128) unsigned int wide_count;       // tail of the wide-item next queue
   alignas(128) unsigned long long edges;      // sum of degrees of the vertices found this level
   alignas(128) unsigned long long bu_count;   // vertices found by a bottom-up level
 };
@@ -84,8 +86,8 @@ struct SearchView {
   int32_t* parent;           // n (vertex ids)
   uint32_t* visited;         // nwords
   uint32_t* bitmap[2];       // frontier / next frontier, nwords each; all-zero while top-down runs
-  int32_t* queue[2];         // n each
-  int32_t* hubq[2];          // hub_cap each
+  int32_t* queue[2];         // narrow rows (degree < kNarrow): vertex ids, n each
+  int2* wideq[2];            // wide rows: (vertex, chunk) work items of <= kChunk entries
   Control* ctl;
 };
 
@@ -93,7 +95,6 @@ struct Tuning {
   int mode;                  // B2BFS_MODE_*
   int alpha;                 // top-down -> bottom-up when m_f > m_u / alpha
   int beta;                  // bottom-up -> top-down when n_f < n / beta
-  int hub_degree;            // vertices at least this wide go to the hub queue
 };
 
 // Level-loop state; a pure function of the counters, so the host (stepwise engine) and every
@@ -103,7 +104,7 @@ struct LoopState {
   int mode;                  // 0 top-down, 1 bottom-up
   int fb;                    // index of the frontier bitmap while bottom-up
   int done;
-  unsigned int cur_q, cur_hub;
+  unsigned int cur_q, cur_wide;
   unsigned long long prev_nf;
   unsigned long long unexplored;  // directed entries whose source is still unvisited
   int td_levels, bu_levels;
@@ -112,8 +113,8 @@ struct LoopState {
 enum Conversion { kNoConversion = 0, kQueueToBitmap = 1, kBitmapToQueue = 2 };
 
 __host__ __device__ inline Conversion advance(LoopState& st, const Tuning& tn, int64_t n, unsigned int nq,
-                                              unsigned int nhub, unsigned long long nbu, unsigned long long mf) {
-  const unsigned long long nf = (st.mode == 0) ? (unsigned long long)nq + nhub : nbu;
+                                              unsigned int nwide, unsigned long long nbu, unsigned long long mf) {
+  const unsigned long long nf = (st.mode == 0) ? (unsigned long long)nq + nwide : nbu;
   if (st.mode == 0) st.td_levels++; else st.bu_levels++;
   st.unexplored = (mf > st.unexplored) ? 0ull : st.unexplored - mf;
   st.level++;
@@ -122,7 +123,7 @@ __host__ __device__ inline Conversion advance(LoopState& st, const Tuning& tn, i
     st.done = 1;
   } else if (st.mode == 0) {
     st.cur_q = nq;
-    st.cur_hub = nhub;
+    st.cur_wide = nwide;
     if (tn.mode == B2BFS_MODE_DIRECTION_OPT && mf > st.unexplored / (unsigned)tn.alpha && nf >= st.prev_nf) {
       st.mode = 1;
       st.fb = 0;
@@ -131,7 +132,7 @@ __host__ __device__ inline Conversion advance(LoopState& st, const Tuning& tn, i
   } else {
     if (nf < (unsigned long long)n / (unsigned)tn.beta && nf < st.prev_nf) {
       st.mode = 0;
-      cv = kBitmapToQueue;  // cur_q / cur_hub are read back after the conversion
+      cv = kBitmapToQueue;  // cur_q / cur_wide are read back after the conversion
     } else {
       st.fb ^= 1;
     }

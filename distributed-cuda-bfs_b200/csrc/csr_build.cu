@@ -173,31 +173,33 @@ __global__ void __launch_bounds__(kBlock) compact_kernel(const uint64_t* __restr
   }
 }
 
-// orig_deg, the "never scan bottom-up" bitmap (degree-0 rows and the padding past n), hub count
+// orig_deg, the "never scan bottom-up" bitmap (degree-0 rows and the padding past n), wide-item count
 __global__ void __launch_bounds__(kBlock) finish_rows_kernel(int64_t nrows, int64_t nwords,
                                                              const int64_t* __restrict__ rowptr,
                                                              const int64_t* __restrict__ orig_rowptr,
                                                              uint32_t* __restrict__ orig_deg,
-                                                             uint32_t* __restrict__ visited_init, int hub_degree,
-                                                             unsigned long long* hub_count,
+                                                             uint32_t* __restrict__ visited_init,
+                                                             unsigned long long* wide_items,
                                                              unsigned long long* max_degree) {
   const int lane = threadIdx.x & 31;
   const int64_t warps = (int64_t)gridDim.x * kWarpsPerBlock;
   unsigned long long mx = 0;
   for (int64_t w = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5); w < nwords; w += warps) {
     const int64_t v = w * 32 + lane;
-    bool skip = true, hub = false;
+    bool skip = true;
+    unsigned long long items = 0;
     if (v < nrows) {
       const int64_t d = rowptr[v + 1] - rowptr[v];
       orig_deg[v] = (uint32_t)(orig_rowptr[v + 1] - orig_rowptr[v]);
       skip = d == 0;
-      hub = d >= hub_degree;
+      if (d >= kNarrow) items = (unsigned long long)((d + kChunk - 1) / kChunk);
       mx = d > (int64_t)mx ? (unsigned long long)d : mx;
     }
-    const unsigned sm = __ballot_sync(0xffffffffu, skip), hm = __ballot_sync(0xffffffffu, hub);
+    const unsigned sm = __ballot_sync(0xffffffffu, skip);
+    for (int o = 16; o; o >>= 1) items += __shfl_down_sync(0xffffffffu, items, o);
     if (lane == 0) {
       visited_init[w] = sm;
-      if (hm) atomicAdd(hub_count, (unsigned long long)__popc(hm));
+      if (items) atomicAdd(wide_items, items);
     }
   }
   for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_down_sync(0xffffffffu, mx, o));
@@ -211,7 +213,7 @@ static int bits_for(int64_t n) {
 }
 
 Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64_t n, int64_t row_begin,
-                        int64_t row_end, bool partitioned, int dedup, int hub_degree, cudaStream_t stream,
+                        int64_t row_end, bool partitioned, int dedup, cudaStream_t stream,
                         BuiltCsr* out, int64_t* launches) {
   *out = BuiltCsr();
   const int64_t nrows = row_end - row_begin;
@@ -221,7 +223,7 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   out->nrows = nrows;
   out->nwords = nwords;
 
-  unsigned long long* counters = nullptr;  // [0] append cursor / owned total, [1] hub count, [2] max degree
+  unsigned long long* counters = nullptr;  // [0] append cursor / owned total, [1] wide items, [2] max degree
   int* bad = nullptr;
   B2_CUDA(cudaMalloc(&counters, 4 * sizeof(unsigned long long)));
   B2_CUDA(cudaMalloc(&bad, sizeof(int)));
@@ -296,13 +298,13 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   const int64_t fblocks = (nwords + kWarpsPerBlock - 1) / kWarpsPerBlock;
   const int fgrid = (int)(fblocks < (int64_t)kSMs * 8 ? fblocks : (int64_t)kSMs * 8);
   finish_rows_kernel<<<fgrid, kBlock, 0, stream>>>(nrows, nwords, out->rowptr, orig_rowptr, out->orig_deg,
-                                                   out->visited_init, hub_degree, counters + 1, counters + 2);
+                                                   out->visited_init, counters + 1, counters + 2);
   if (launches) *launches += 1;
   unsigned long long hc[2] = {0, 0};
   B2_CUDA(cudaMemcpyAsync(hc, counters + 1, sizeof(hc), cudaMemcpyDeviceToHost, stream));
   B2_CUDA(cudaStreamSynchronize(stream));
   B2_CUDA(cudaGetLastError());
-  out->num_hubs = (int64_t)hc[0];
+  out->wide_items = (int64_t)hc[0];
   out->max_degree = (int64_t)hc[1];
 
   cudaFree(orig_rowptr);
