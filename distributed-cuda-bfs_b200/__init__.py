@@ -17,7 +17,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb2bfs.so")
+LIB_PATH = os.environ.get("B2BFS_LIB", os.path.join(_HERE, "lib", "libb2bfs.so"))  # override: A/B builds only
 CLI_PATH = os.path.join(_HERE, "bin", "b2bfs")
 HEADER_PATH = os.path.abspath(os.path.join(_HERE, "..", "include", "b2bfs.h"))
 
@@ -85,6 +85,7 @@ def lib() -> C.CDLL:
             "b2bfs_run_device": ([vp, i64, C.POINTER(Stats)], C.c_int),
             "b2bfs_device_depth": ([vp, C.POINTER(vp)], C.c_int),
             "b2bfs_device_parent": ([vp, C.POINTER(vp)], C.c_int),
+            "b2bfs_last_trace": ([vp, vp, vp, vp, C.c_int], C.c_int),
             "b2bfs_host_alloc": ([C.POINTER(vp), i64], C.c_int),
             "b2bfs_host_free": ([vp], C.c_int),
             "b2bfs_destroy": ([vp], C.c_int),
@@ -230,6 +231,16 @@ class Bfs:
         st = Stats()
         self._check(lib().b2bfs_run_device(self._h, int(src), C.byref(st)))
         return st.as_dict()
+
+    def last_trace(self, cap: int = 96):
+        """[(level, phase, microseconds since kernel start)] of the last fused search."""
+        lv = np.empty(cap, np.int32)
+        ph = np.empty(cap, np.int32)
+        us = np.empty(cap, np.float64)
+        n = lib().b2bfs_last_trace(self._h, lv.ctypes.data, ph.ctypes.data, us.ctypes.data, cap)
+        if n < 0:
+            raise B2BfsError(n, "b2bfs_last_trace")
+        return [(int(lv[i]), int(ph[i]), float(us[i])) for i in range(n)]
 
     def device_depth_ptr(self) -> int:
         p = C.c_void_p()

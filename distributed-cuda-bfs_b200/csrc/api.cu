@@ -373,6 +373,20 @@ int b2bfs_device_parent(const b2bfs_t* h, const int32_t** parent_dev) {
   return B2BFS_OK;
 }
 
+int b2bfs_last_trace(b2bfs_t* h, int32_t* level_out, int32_t* phase_out, double* us_out, int cap) {
+  if (!h || !h->has_graph || cap < 0) return B2BFS_ERR_ARG;
+  if (cudaSetDevice(h->device) != cudaSuccess) return B2BFS_ERR_CUDA;
+  if (cudaMemcpy(h->pinned_ctl, h->sv.ctl, sizeof(Control), cudaMemcpyDeviceToHost) != cudaSuccess) return B2BFS_ERR_CUDA;
+  const Control* c = h->pinned_ctl;
+  int n = c->trace_len < cap ? c->trace_len : cap;
+  for (int i = 0; i < n; ++i) {
+    level_out[i] = c->trace[i].level;
+    phase_out[i] = c->trace[i].phase;
+    us_out[i] = (double)(c->trace[i].t_ns - c->trace[0].t_ns) * 1e-3;
+  }
+  return n;
+}
+
 int b2bfs_host_alloc(void** p, int64_t bytes) {
   if (!p || bytes < 0) return B2BFS_ERR_ARG;
   return cudaMallocHost(p, (size_t)(bytes > 0 ? bytes : 1)) == cudaSuccess ? B2BFS_OK : B2BFS_ERR_NOMEM;

@@ -23,7 +23,6 @@ namespace cg = cooperative_groups;
 
 namespace b2 {
 
-constexpr int kBuProbe = 4;          // neighbours a bottom-up lane checks alone before its warp helps
 constexpr int kStageFlush = 160;     // a warp flushes its staging buffer once it holds this many ids
 constexpr int kStageCap = kStageFlush + 128;  // + at most 4 discoveries per lane between two checks
 
@@ -90,6 +89,7 @@ __device__ __forceinline__ void stage_flush(WarpStage& sg, LevelSlot* ns, int32_
     for (int i0 = 0; i0 < wc; i0 += 32) {  // one tail atomic per 32 staged rows
       const int i = i0 + (int)lane;
       const unsigned items = i < wc ? (unsigned)sg.witems[i] : 0u;
+      const int32_t v = i < wc ? sg.wide[i] : 0;
       unsigned incl = items;
       for (int o = 1; o < 32; o <<= 1) {
         const unsigned y = __shfl_up_sync(0xffffffffu, incl, o);
@@ -98,9 +98,16 @@ __device__ __forceinline__ void stage_flush(WarpStage& sg, LevelSlot* ns, int32_
       unsigned base = 0;
       if (lane == 31) base = atomicAdd(&ns->wide_count, incl);
       base = __shfl_sync(0xffffffffu, base, 31) + incl - items;
-      if (items) {
-        const int32_t v = sg.wide[i];
+      if (items && items <= 8) {
         for (unsigned c = 0; c < items; ++c) nwq[base + c] = make_int2(v, (int)c);
+      }
+      unsigned big = __ballot_sync(0xffffffffu, items > 8);  // long rows: the whole warp writes the items
+      while (big) {
+        const int l = __ffs(big) - 1;
+        big &= big - 1;
+        const unsigned bi = __shfl_sync(0xffffffffu, items, l), bb = __shfl_sync(0xffffffffu, base, l);
+        const int32_t bv = __shfl_sync(0xffffffffu, v, l);
+        for (unsigned c = lane; c < bi; c += 32) nwq[bb + c] = make_int2(bv, (int)c);
       }
     }
     __syncwarp();
@@ -113,7 +120,7 @@ __device__ __forceinline__ void stage_flush(WarpStage& sg, LevelSlot* ns, int32_
 // per-search reset (fused: depth/parent fill, visited := visited_init, bitmaps := 0, seed)
 // algorithmic bytes: 8n written (depth + parent) + 3n/8 bitmap bytes
 // ---------------------------------------------------------------------------------------------
-__device__ void phase_init(const BfsParams& p, int64_t src) {
+__device__ __forceinline__ void phase_init(const BfsParams& p, int64_t src) {
   const int64_t tid = (int64_t)blockIdx.x * kBlock + threadIdx.x;
   const int64_t nthreads = (int64_t)gridDim.x * kBlock;
   const int64_t n = p.g.n, n4 = n >> 2;
@@ -174,6 +181,8 @@ __device__ void phase_init(const BfsParams& p, int64_t src) {
     }
     c->result.levels = c->result.td_levels = c->result.bu_levels = 0;
     c->src_degree = deg;
+    c->group_barrier = 0;
+    c->group_exit_seq = 0;
   }
 }
 
@@ -203,20 +212,39 @@ __host__ __device__ inline LoopState initial_state(const BfsParams& p, int64_t s
 // algorithmic bytes per level: 4 B per frontier vertex / 8 B per item + 16 B row extent + 4 B per
 // neighbour entry; per discovered vertex 8 B (depth + parent) + 16 B its row extent + 4-8 B queue
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void td_visit(const BfsParams& p, int level, WarpStage& sg, int32_t v, int32_t u,
-                                         unsigned long long& edges_acc) {
-  const uint32_t w = (uint32_t)v >> 5, bit = 1u << (v & 31);
+// Four (u -> v) entries per lane at a time, phase by phase, so that the four visited probes, the
+// four claims and the four row-extent reads are each in flight together instead of forming one
+// long dependent chain per entry.
+__device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpStage& sg, const int32_t (&v)[4],
+                                          const int32_t (&u)[4], const bool (&valid)[4],
+                                          unsigned long long& edges_acc) {
+  uint32_t word[4];
+  bool c[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) word[k] = valid[k] ? p.s.visited[(uint32_t)v[k] >> 5] : 0xffffffffu;
   // cheap read first; a stale "clear" only costs one extra atomic (bits only go 0 -> 1 in a search)
-  if (p.s.visited[w] & bit) return;
-  if (atomicOr(&p.s.visited[w], bit) & bit) return;
-  p.s.depth[v] = level + 1;
-  p.s.parent[v] = u;
-  const int64_t d = __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v);
-  edges_acc += (unsigned long long)d;
-  route_vertex(sg, v, d);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) c[k] = !((word[k] >> (v[k] & 31)) & 1u);
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (c[k]) word[k] = atomicOr(&p.s.visited[(uint32_t)v[k] >> 5], 1u << (v[k] & 31));
+#pragma unroll
+  for (int k = 0; k < 4; ++k) c[k] = c[k] && !((word[k] >> (v[k] & 31)) & 1u);
+  int64_t d[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) d[k] = c[k] ? __ldg(p.g.rowptr + v[k] + 1) - __ldg(p.g.rowptr + v[k]) : 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (c[k]) {
+      p.s.depth[v[k]] = level + 1;
+      p.s.parent[v[k]] = u[k];
+      edges_acc += (unsigned long long)d[k];
+      route_vertex(sg, v[k], d[k]);
+    }
+  }
 }
 
-__device__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStage* stage) {
+__device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStage* stage, int bid, int nb) {
   const int level = st.level;
   const int32_t* q = p.s.queue[level & 1];
   const int2* wq = p.s.wideq[level & 1];
@@ -225,12 +253,12 @@ __device__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStag
   LevelSlot* ns = &p.s.ctl->slot[(level + 1) & 3];
   const unsigned lane = lane_id();
   WarpStage& sg = stage[threadIdx.x >> 5];
-  const int64_t gw = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-  const int64_t nwarps = (int64_t)gridDim.x * kWarpsPerBlock;
+  const int64_t gw = (int64_t)bid * kWarpsPerBlock + (threadIdx.x >> 5);
+  const int64_t nwarps = (int64_t)nb * kWarpsPerBlock;
   unsigned long long edges_acc = 0;
 
   if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {  // recycle the slot two levels ahead
+  if (bid == 0 && threadIdx.x == 0) {  // recycle the slot two levels ahead
     LevelSlot* z = &p.s.ctl->slot[(level + 2) & 3];
     z->q_count = 0; z->wide_count = 0; z->edges = 0; z->bu_count = 0;
   }
@@ -242,7 +270,7 @@ __device__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStag
     if (item < tiles) {
       const int64_t idx = item * 32 + lane;
       const bool has = idx < (int64_t)st.cur_q;
-      const int32_t u = has ? q[idx] : 0;
+      const int32_t u = has ? __ldcg(q + idx) : 0;  // written last level by other SMs: read at L2
       int64_t rs = 0;
       uint32_t d = 0;
       if (has) {
@@ -256,23 +284,30 @@ __device__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStag
       }
       const uint32_t excl = incl - d;
       const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-      for (uint32_t base = 0; base < total; base += 32) {
-        const uint32_t k = base + lane;
-        int lo = 0, hi = 31;  // owner = largest lane whose exclusive prefix is <= k
+      for (uint32_t base = 0; base < total; base += 128) {  // 4 entries per lane per step
+        int32_t v[4], uu[4];
+        bool valid[4];
 #pragma unroll
-        for (int s = 0; s < 5; ++s) {
-          const int mid = (lo + hi + 1) >> 1;
-          const uint32_t val = __shfl_sync(0xffffffffu, excl, mid);
-          if (val <= k) lo = mid; else hi = mid - 1;
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t k = base + 32 * j + lane;
+          int lo = 0, hi = 31;  // owner = largest lane whose exclusive prefix is <= k
+#pragma unroll
+          for (int s = 0; s < 5; ++s) {
+            const int mid = (lo + hi + 1) >> 1;
+            const uint32_t val = __shfl_sync(0xffffffffu, excl, mid);
+            if (val <= k) lo = mid; else hi = mid - 1;
+          }
+          const uint32_t oe = __shfl_sync(0xffffffffu, excl, lo);
+          const int64_t ors = __shfl_sync(0xffffffffu, rs, lo);
+          uu[j] = __shfl_sync(0xffffffffu, u, lo);
+          valid[j] = k < total;
+          v[j] = valid[j] ? __ldg(p.g.col + ors + (k - oe)) : 0;
         }
-        const uint32_t oe = __shfl_sync(0xffffffffu, excl, lo);
-        const int64_t ors = __shfl_sync(0xffffffffu, rs, lo);
-        const int32_t uu = __shfl_sync(0xffffffffu, u, lo);
-        if (k < total) td_visit(p, level, sg, __ldg(p.g.col + ors + (k - oe)), uu, edges_acc);
+        td_visit4(p, level, sg, v, uu, valid, edges_acc);
         stage_flush(sg, ns, nq, nwq, false);
       }
     } else {
-      const int2 it = wq[item - tiles];
+      const int2 it = __ldcg(wq + (item - tiles));
       const int32_t u = it.x;
       const int64_t rs = __ldg(p.g.rowptr + u) + (int64_t)it.y * kChunk;
       const int64_t re = min(__ldg(p.g.rowptr + u + 1), rs + kChunk);
@@ -281,10 +316,11 @@ __device__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStag
         const int64_t base = b0 + 4 * lane;
         if (base < re) {
           const int4 x = __ldg(reinterpret_cast<const int4*>(p.g.col + base));
-          if (base >= rs) td_visit(p, level, sg, x.x, u, edges_acc);
-          if (base + 1 >= rs && base + 1 < re) td_visit(p, level, sg, x.y, u, edges_acc);
-          if (base + 2 >= rs && base + 2 < re) td_visit(p, level, sg, x.z, u, edges_acc);
-          if (base + 3 >= rs && base + 3 < re) td_visit(p, level, sg, x.w, u, edges_acc);
+          const int32_t v[4] = {x.x, x.y, x.z, x.w};
+          const int32_t uu[4] = {u, u, u, u};
+          const bool valid[4] = {base >= rs, base + 1 >= rs && base + 1 < re, base + 2 >= rs && base + 2 < re,
+                                 base + 3 >= rs && base + 3 < re};
+          td_visit4(p, level, sg, v, uu, valid, edges_acc);
         }
         stage_flush(sg, ns, nq, nwq, false);
       }
@@ -295,74 +331,149 @@ __device__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStag
 }
 
 // ---------------------------------------------------------------------------------------------
-// bottom-up: one warp per visited-bitmap word (32 consecutive vertices), one lane per vertex.
-// A lane probes its first kBuProbe neighbours alone; rows still unresolved after that are finished
-// by the whole warp with coalesced reads and an early exit on the first frontier neighbour.
-// The next-frontier word and the visited word are written once per warp with plain stores.
+// bottom-up.  One visited-bitmap WORD PER LANE: a warp reads 32 words with one coalesced load and
+// every lane walks the unvisited vertices of its own word, so all 32 lanes stay busy whether 60 %
+// (first bottom-up level) or 1 % (later levels) of the vertices are unvisited.  The walk is a
+// four-stage software pipeline — per round a lane (A) requests the row extent of its next vertex,
+// (B) requests the first kBuFirst neighbour ids of the vertex from the round before, (C) requests
+// the frontier-bitmap words for the neighbours loaded the round before that, and (D) looks at the
+// answers of the round before that — so no round waits on a load it issued itself: the
+// rowptr -> col -> bitmap chain (2 DRAM + 1 L2 latency) overlaps across consecutive vertices.
+// Vertices not settled by their first kBuFirst neighbours go to a per-warp list in shared memory
+// and are finished four at a time by 8-lane groups with coalesced 32-byte reads and early exit.
+// Next-frontier and visited words are written once, by the lane that owns them, coalesced.
 // algorithmic bytes per level: n/8 (visited) + n/8 (next) + 16 B per unvisited vertex (row extent)
-// + 4 B per neighbour entry inspected + 8 B per discovered vertex; frontier probes hit L2.
+// + 4 B per neighbour entry inspected + 8 B per discovered vertex; frontier probes hit L1/L2.
 // ---------------------------------------------------------------------------------------------
-__device__ void phase_bottom_up(const BfsParams& p, const LoopState& st) {
+constexpr int kBuFirst = 2;      // neighbours probed in the pipelined pass
+constexpr int kBuDeferFlush = kStageCap - 32;
+
+// finish the listed vertices: 8 lanes per vertex, 8 entries per step
+__device__ __forceinline__ void bu_finish_deferred(const BfsParams& p, int level, const uint32_t* fr, WarpStage& sg,
+                                                   int64_t w0, unsigned long long& edges_acc) {
+  __syncwarp();
+  const unsigned lane = lane_id();
+  const int cnt = *reinterpret_cast<volatile int*>(&sg.ncnt);
+  const int g = lane >> 3, gl = lane & 7;
+  for (int base = 0; base < cnt; base += 4) {
+    const int idx = base + g;
+    const bool has = idx < cnt;
+    const int32_t v = has ? sg.narrow[idx] : 0;
+    int64_t r0 = 0, re = 0;
+    if (has) {
+      r0 = __ldg(p.g.rowptr + v);
+      re = __ldg(p.g.rowptr + v + 1);
+    }
+    int64_t pos = r0 + kBuFirst;
+    bool active = has && pos < re;
+    int32_t par = -1;
+    while (__ballot_sync(0xffffffffu, active)) {
+      const int64_t i = pos + gl;
+      const bool a = active && i < re;
+      const int32_t u = a ? __ldg(p.g.col + i) : 0;
+      const unsigned bm = __ballot_sync(0xffffffffu, a && test_bit(fr, u));
+      const unsigned gm = (bm >> (g * 8)) & 0xffu;
+      const int32_t pu = __shfl_sync(0xffffffffu, u, gm ? g * 8 + __ffs(gm) - 1 : (int)lane);
+      if (active) {
+        if (gm) {
+          par = pu;
+          active = false;
+        } else {
+          pos += 8;
+          active = pos < re;
+        }
+      }
+    }
+    if (has && gl == 0 && par >= 0) {
+      p.s.depth[v] = level + 1;
+      p.s.parent[v] = par;
+      atomicOr(reinterpret_cast<unsigned int*>(&sg.wide[((int64_t)v >> 5) - w0]), 1u << (v & 31));
+      edges_acc += (unsigned long long)(re - r0);
+    }
+  }
+  __syncwarp();
+  if (lane == 0) sg.ncnt = 0;
+  __syncwarp();
+}
+
+__device__ __forceinline__ void phase_bottom_up(const BfsParams& p, const LoopState& st, WarpStage* stage) {
   const int level = st.level;
   const uint32_t* fr = p.s.bitmap[st.fb];
   uint32_t* nx = p.s.bitmap[st.fb ^ 1];
   LevelSlot* ns = &p.s.ctl->slot[(level + 1) & 3];
   const unsigned lane = lane_id();
+  WarpStage& sg = stage[threadIdx.x >> 5];  // narrow[] = deferred list, wide[0..31] = found bits per word
   const int64_t gw = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)gridDim.x * kWarpsPerBlock;
-  const int64_t n = p.g.n;
   unsigned long long edges_acc = 0, count_acc = 0;
 
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     LevelSlot* z = &p.s.ctl->slot[(level + 2) & 3];
     z->q_count = 0; z->wide_count = 0; z->edges = 0; z->bu_count = 0;
   }
+  if (lane == 0) sg.ncnt = 0;
+  sg.wide[lane] = 0;
+  __syncwarp();
 
-  for (int64_t w = gw; w < p.g.nwords; w += nwarps) {
-    const uint32_t vis = p.s.visited[w];
-    if (vis == 0xffffffffu) {
-      if (lane == 0) nx[w] = 0;
-      continue;
-    }
-    const int64_t v = w * 32 + lane;
-    const bool act = !((vis >> lane) & 1u);
-    const int64_t vc = v < n ? v : n - 1;  // padding lanes are never active; keep their loads in range
-    const int64_t rs = __ldg(p.g.rowptr + vc), re = __ldg(p.g.rowptr + vc + 1);
-    bool found = false;
-    int32_t par = -1;
-    if (act) {
-      const int64_t lim = min(re, rs + kBuProbe);
-      for (int64_t i = rs; i < lim; ++i) {
-        const int32_t u = __ldg(p.g.col + i);
-        if (test_bit(fr, u)) { found = true; par = u; break; }
+  for (int64_t w0 = gw * 32; w0 < p.g.nwords; w0 += nwarps * 32) {
+    const int64_t w = w0 + lane;
+    const bool inr = w < p.g.nwords;
+    const uint32_t vis = inr ? p.s.visited[w] : 0xffffffffu;
+    uint32_t todo = ~vis, found_bits = 0;
+    int bA = -1, bB = -1, bC = -1;
+    int64_t rsA = 0, reA = 0, rsB = 0, nC = 0;
+    int64_t nB = 0;
+    int32_t uB0 = 0, uB1 = 0, uC0 = 0, uC1 = 0;
+    uint32_t pw0 = 0, pw1 = 0;
+    while (__ballot_sync(0xffffffffu, (todo != 0) | (bA >= 0) | (bB >= 0) | (bC >= 0))) {
+      // D: answers for the vertex probed last round
+      if (bC >= 0) {
+        const bool h0 = (pw0 >> (uC0 & 31)) & 1u;
+        const bool h1 = nC > 1 && ((pw1 >> (uC1 & 31)) & 1u);
+        const int64_t v = w * 32 + bC;
+        if (h0 | h1) {
+          p.s.depth[v] = level + 1;
+          p.s.parent[v] = h0 ? uC0 : uC1;
+          found_bits |= 1u << bC;
+          edges_acc += (unsigned long long)nC;
+        } else if (nC > kBuFirst) {
+          sg.narrow[atomicAdd(&sg.ncnt, 1)] = (int32_t)v;
+        }
       }
-    }
-    unsigned pend = __ballot_sync(0xffffffffu, act && !found && rs + kBuProbe < re);
-    while (pend) {
-      const int l = __ffs(pend) - 1;
-      pend &= pend - 1;
-      const int64_t ss = __shfl_sync(0xffffffffu, rs, l) + kBuProbe, ee = __shfl_sync(0xffffffffu, re, l);
-      int32_t hit_par = -1;
-      for (int64_t base = ss; base < ee; base += 32) {
-        const int64_t i = base + lane;
-        const bool a = i < ee;
-        const int32_t u = a ? __ldg(p.g.col + i) : 0;
-        const unsigned hm = __ballot_sync(0xffffffffu, a && test_bit(fr, u));
-        if (hm) { hit_par = __shfl_sync(0xffffffffu, u, __ffs(hm) - 1); break; }
+      // C: request frontier words for the neighbours that arrived
+      bC = bB; nC = nB; uC0 = uB0; uC1 = uB1;
+      if (bC >= 0) {
+        pw0 = fr[(uint32_t)uC0 >> 5];
+        pw1 = fr[(uint32_t)uC1 >> 5];
       }
-      if ((int)lane == l && hit_par >= 0) { found = true; par = hit_par; }
+      // B: request the first neighbours of the row whose extent arrived
+      bB = bA; rsB = rsA; nB = reA - rsA;
+      if (bB >= 0) {
+        uB0 = __ldg(p.g.col + rsB);
+        uB1 = __ldg(p.g.col + rsB + (nB > 1 ? 1 : 0));
+      }
+      // A: request the extent of the next unvisited vertex of this lane's word
+      if (todo) {
+        bA = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int64_t v = w * 32 + bA;
+        rsA = __ldg(p.g.rowptr + v);
+        reA = __ldg(p.g.rowptr + v + 1);
+      } else {
+        bA = -1;
+      }
+      __syncwarp();
+      if (*reinterpret_cast<volatile int*>(&sg.ncnt) >= kBuDeferFlush) bu_finish_deferred(p, level, fr, sg, w0, edges_acc);
     }
-    const unsigned fm = __ballot_sync(0xffffffffu, found);
-    if (found) {
-      p.s.depth[v] = level + 1;
-      p.s.parent[v] = par;
-      edges_acc += (unsigned long long)(re - rs);
+    bu_finish_deferred(p, level, fr, sg, w0, edges_acc);
+    found_bits |= (uint32_t)sg.wide[lane];
+    sg.wide[lane] = 0;
+    if (inr) {
+      nx[w] = found_bits;
+      if (found_bits) p.s.visited[w] = vis | found_bits;
+      count_acc += __popc(found_bits);
     }
-    if (lane == 0) {
-      nx[w] = fm;
-      if (fm) p.s.visited[w] = vis | fm;
-      count_acc += __popc(fm);
-    }
+    __syncwarp();
   }
   block_accumulate(edges_acc, &ns->edges);
   block_accumulate(count_acc, &ns->bu_count);
@@ -372,7 +483,7 @@ __device__ void phase_bottom_up(const BfsParams& p, const LoopState& st) {
 // representation changes at a direction switch
 // ---------------------------------------------------------------------------------------------
 // work lists of the new frontier (level st.level) -> bitmap[0]; both bitmaps are all-zero on entry
-__device__ void phase_queue_to_bitmap(const BfsParams& p, const LoopState& st) {
+__device__ __forceinline__ void phase_queue_to_bitmap(const BfsParams& p, const LoopState& st) {
   const int32_t* q = p.s.queue[st.level & 1];
   const int2* wq = p.s.wideq[st.level & 1];
   uint32_t* bm = p.s.bitmap[0];
@@ -390,7 +501,7 @@ __device__ void phase_queue_to_bitmap(const BfsParams& p, const LoopState& st) {
 // next bitmap (written by the bottom-up level that just ended) -> work lists of level st.level,
 // routed by degree through the same per-warp staging; clears both bitmaps so the "all-zero while
 // top-down" invariant holds again
-__device__ void phase_bitmap_to_queue(const BfsParams& p, const LoopState& st, WarpStage* stage) {
+__device__ __forceinline__ void phase_bitmap_to_queue(const BfsParams& p, const LoopState& st, WarpStage* stage) {
   uint32_t* nx = p.s.bitmap[st.fb ^ 1];
   uint32_t* fr = p.s.bitmap[st.fb];
   int32_t* q = p.s.queue[st.level & 1];
@@ -402,20 +513,28 @@ __device__ void phase_bitmap_to_queue(const BfsParams& p, const LoopState& st, W
   __syncwarp();
   const int64_t gw = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
   const int64_t nwarps = (int64_t)gridDim.x * kWarpsPerBlock;
-  for (int64_t w = gw; w < p.g.nwords; w += nwarps) {
+  // one bitmap word per LANE (coalesced 128-byte reads and clears); set bits are peeled four per
+  // lane per round so a warp never stages more than 128 ids between two flush checks
+  for (int64_t w0 = gw * 32; w0 < p.g.nwords; w0 += nwarps * 32) {
+    const int64_t w = w0 + lane;
     uint32_t bits = 0;
-    if (lane == 0) {
+    if (w < p.g.nwords) {
       bits = nx[w];
       nx[w] = 0;
       fr[w] = 0;
     }
-    bits = __shfl_sync(0xffffffffu, bits, 0);
-    if (!bits) continue;
-    if ((bits >> lane) & 1u) {
-      const int64_t v = w * 32 + lane;
-      route_vertex(sg, (int32_t)v, __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v));
+    while (__ballot_sync(0xffffffffu, bits != 0)) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (bits) {
+          const int b = __ffs(bits) - 1;
+          bits &= bits - 1;
+          const int64_t v = w * 32 + b;
+          route_vertex(sg, (int32_t)v, __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v));
+        }
+      }
+      stage_flush(sg, cs, q, wq, false);
     }
-    stage_flush(sg, cs, q, wq, false);
   }
   stage_flush(sg, cs, q, wq, true);
 }
@@ -426,9 +545,12 @@ __device__ void phase_bitmap_to_queue(const BfsParams& p, const LoopState& st, W
 __global__ void __launch_bounds__(kBlock) search_init_kernel(BfsParams p, int64_t src) { phase_init(p, src); }
 __global__ void __launch_bounds__(kBlock) top_down_kernel(BfsParams p, LoopState st) {
   __shared__ WarpStage stage[kWarpsPerBlock];
-  phase_top_down(p, st, stage);
+  phase_top_down(p, st, stage, blockIdx.x, gridDim.x);
 }
-__global__ void __launch_bounds__(kBlock) bottom_up_kernel(BfsParams p, LoopState st) { phase_bottom_up(p, st); }
+__global__ void __launch_bounds__(kBlock) bottom_up_kernel(BfsParams p, LoopState st) {
+  __shared__ WarpStage stage[kWarpsPerBlock];
+  phase_bottom_up(p, st, stage);
+}
 __global__ void __launch_bounds__(kBlock) queue_to_bitmap_kernel(BfsParams p, LoopState st) {
   phase_queue_to_bitmap(p, st);
 }
@@ -450,24 +572,104 @@ __device__ __forceinline__ unsigned long long ld_volatile(const unsigned long lo
   return *reinterpret_cast<const volatile unsigned long long*>(p);
 }
 
-__global__ void __launch_bounds__(kBlock) bfs_fused_kernel(BfsParams p, int64_t src) {
+// Small frontiers (the first and last levels of a power-law search, EVERY level of a grid or road
+// graph): a full-grid barrier per level costs more than the level.  The first kGroupBlocks CTAs
+// then run consecutive top-down levels on their own, separated by a 16-party barrier on one global
+// counter, while the other CTAs wait at the next grid-wide barrier.
+#ifndef B2_FUSED_MIN_BLOCKS
+#define B2_FUSED_MIN_BLOCKS 4  // resident CTAs per SM the fused kernel is register-capped for
+#endif
+constexpr int kGroupBlocks = 16;
+constexpr unsigned kGroupMaxWork = kGroupBlocks * kWarpsPerBlock * 2;  // tiles + items per level
+
+__device__ __forceinline__ unsigned frontier_work(const LoopState& st) { return ((st.cur_q + 31u) >> 5) + st.cur_wide; }
+
+__device__ __forceinline__ void group_barrier(unsigned long long* counter, unsigned long long& epoch, int parties) {
+  epoch += (unsigned long long)parties;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();  // publish this CTA's queue writes
+    atomicAdd(counter, 1ull);
+    while (ld_volatile(counter) < epoch) {}
+    __threadfence();  // and drop stale L1 lines before anyone reads what the others wrote
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void trace_mark(Control* c, int& n, int level, int phase) {
+  if (blockIdx.x == 0 && threadIdx.x == 0 && n < kTraceCap) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    c->trace[n].level = level;
+    c->trace[n].phase = phase;
+    c->trace[n].t_ns = t;
+    c->trace_len = ++n;
+  }
+}
+
+__global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(BfsParams p, int64_t src) {
   __shared__ WarpStage stage[kWarpsPerBlock];
   cg::grid_group grid = cg::this_grid();
   phase_init(p, src);
   LoopState st = initial_state(p, __ldg(p.g.rowptr + src + 1) - __ldg(p.g.rowptr + src));
+  const int group = min((int)gridDim.x, kGroupBlocks);
+  unsigned long long epoch = 0;
+  unsigned int group_seq = 0;
+  int ntrace = 0;
+  trace_mark(p.s.ctl, ntrace, 0, -1);
   grid.sync();
+  trace_mark(p.s.ctl, ntrace, 0, 0);
   while (!st.done) {
-    if (st.mode == 0) phase_top_down(p, st, stage); else phase_bottom_up(p, st);
-    grid.sync();
-    const LevelSlot* ns = &p.s.ctl->slot[(st.level + 1) & 3];
-    const Conversion cv = advance(st, p.tn, p.g.n, ld_volatile(&ns->q_count), ld_volatile(&ns->wide_count),
-                                  ld_volatile(&ns->bu_count), ld_volatile(&ns->edges));
+    Conversion cv = kNoConversion;
+    if (st.mode == 0 && frontier_work(st) <= kGroupMaxWork) {
+      ++group_seq;
+      if ((int)blockIdx.x < group) {
+        do {
+          phase_top_down(p, st, stage, blockIdx.x, group);
+          group_barrier(&p.s.ctl->group_barrier, epoch, group);
+          const LevelSlot* ns = &p.s.ctl->slot[(st.level + 1) & 3];
+          cv = advance(st, p.tn, p.g.n, ld_volatile(&ns->q_count), ld_volatile(&ns->wide_count),
+                       ld_volatile(&ns->bu_count), ld_volatile(&ns->edges));
+        } while (!st.done && cv == kNoConversion && frontier_work(st) <= kGroupMaxWork);
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+          p.s.ctl->resume_state = st;
+          p.s.ctl->resume_conversion = (int)cv;
+          __threadfence();
+          *reinterpret_cast<volatile unsigned int*>(&p.s.ctl->group_exit_seq) = group_seq;
+        }
+      } else {
+        // the other CTAs sleep on a flag instead of hammering the grid barrier's L2 line for
+        // what can be thousands of levels
+        if (threadIdx.x == 0)
+          while (ld_volatile(&p.s.ctl->group_exit_seq) < group_seq) __nanosleep(2000);
+        __syncthreads();
+      }
+      grid.sync();
+      if ((int)blockIdx.x >= group) {  // catch up with what the group decided
+        const volatile LoopState* rs = &p.s.ctl->resume_state;
+        st.level = rs->level; st.mode = rs->mode; st.fb = rs->fb; st.done = rs->done;
+        st.cur_q = rs->cur_q; st.cur_wide = rs->cur_wide; st.prev_nf = rs->prev_nf;
+        st.unexplored = rs->unexplored; st.td_levels = rs->td_levels; st.bu_levels = rs->bu_levels;
+        cv = (Conversion)(*reinterpret_cast<const volatile int*>(&p.s.ctl->resume_conversion));
+      }
+      trace_mark(p.s.ctl, ntrace, st.level, 5);
+    } else {
+      const int ph = st.mode == 0 ? 1 : 2;
+      if (st.mode == 0) phase_top_down(p, st, stage, blockIdx.x, gridDim.x); else phase_bottom_up(p, st, stage);
+      grid.sync();
+      trace_mark(p.s.ctl, ntrace, st.level, ph);
+      const LevelSlot* ns = &p.s.ctl->slot[(st.level + 1) & 3];
+      cv = advance(st, p.tn, p.g.n, ld_volatile(&ns->q_count), ld_volatile(&ns->wide_count),
+                   ld_volatile(&ns->bu_count), ld_volatile(&ns->edges));
+    }
     if (cv == kQueueToBitmap) {
       phase_queue_to_bitmap(p, st);
       grid.sync();
+      trace_mark(p.s.ctl, ntrace, st.level, 3);
     } else if (cv == kBitmapToQueue) {
       phase_bitmap_to_queue(p, st, stage);
       grid.sync();
+      trace_mark(p.s.ctl, ntrace, st.level, 4);
       const LevelSlot* cs = &p.s.ctl->slot[st.level & 3];
       st.cur_q = ld_volatile(&cs->q_count);
       st.cur_wide = ld_volatile(&cs->wide_count);

@@ -74,11 +74,36 @@ struct SearchResult {
   int32_t levels, td_levels, bu_levels, pad;
 };
 
+// Level-loop state; a pure function of the counters, so the host (stepwise engine) and every
+// thread of the persistent kernel (fused engine) compute the same decisions.
+struct LoopState {
+  int level;
+  int mode;                  // 0 top-down, 1 bottom-up
+  int fb;                    // index of the frontier bitmap while bottom-up
+  int done;
+  unsigned int cur_q, cur_wide;
+  unsigned long long prev_nf;
+  unsigned long long unexplored;  // directed entries whose source is still unvisited
+  int td_levels, bu_levels;
+};
+
+constexpr int kTraceCap = 96;
+struct TraceRec {
+  int level, phase;            // phase: 0 reset, 1 top-down, 2 bottom-up, 3 queue->bitmap, 4 bitmap->queue, 5 group levels
+  unsigned long long t_ns;     // %globaltimer when CTA 0 left the phase's barrier
+};
+
 struct Control {
   LevelSlot slot[4];         // ring indexed by level & 3
   SearchResult result;
   int64_t src_degree;        // written by the reset phase (the stepwise host loop starts from it)
   unsigned long long reached_vertices, reached_entries;  // filled by reach_stats_kernel
+  alignas(128) unsigned long long group_barrier;         // monotonic arrival counter of the small-frontier group
+  alignas(128) LoopState resume_state;                   // what the group decided, for the CTAs that waited
+  int resume_conversion;
+  unsigned int group_exit_seq;                           // bumped when the group leaves its level loop
+  int trace_len;                                         // fused engine: per-phase timestamps of CTA 0
+  TraceRec trace[kTraceCap];
 };
 
 struct SearchView {
@@ -95,19 +120,6 @@ struct Tuning {
   int mode;                  // B2BFS_MODE_*
   int alpha;                 // top-down -> bottom-up when m_f > m_u / alpha
   int beta;                  // bottom-up -> top-down when n_f < n / beta
-};
-
-// Level-loop state; a pure function of the counters, so the host (stepwise engine) and every
-// thread of the persistent kernel (fused engine) compute the same decisions.
-struct LoopState {
-  int level;
-  int mode;                  // 0 top-down, 1 bottom-up
-  int fb;                    // index of the frontier bitmap while bottom-up
-  int done;
-  unsigned int cur_q, cur_wide;
-  unsigned long long prev_nf;
-  unsigned long long unexplored;  // directed entries whose source is still unvisited
-  int td_levels, bu_levels;
 };
 
 enum Conversion { kNoConversion = 0, kQueueToBitmap = 1, kBitmapToQueue = 2 };

@@ -131,6 +131,12 @@ int b2bfs_run_device(b2bfs_t* h, int64_t src, b2bfs_stats* stats);
 int b2bfs_device_depth(const b2bfs_t* h, const int32_t** depth_dev);
 int b2bfs_device_parent(const b2bfs_t* h, const int32_t** parent_dev);
 
+/* Diagnostics: per-phase timestamps of the last fused search (level, phase code, microseconds since
+ * the kernel started; phase codes: -1 start, 0 reset, 1 top-down, 2 bottom-up, 3 queue->bitmap,
+ * 4 bitmap->queue, 5 a run of small-frontier levels).  Returns the number of records written
+ * (<= cap) or a negative error.  Stands in for the commented-out per-level printf at bfs.cu:576. */
+int b2bfs_last_trace(b2bfs_t* h, int32_t* level_out, int32_t* phase_out, double* us_out, int cap);
+
 /* Page-locked host memory for callers that want the copies in b2bfs_run at full PCIe speed. */
 int b2bfs_host_alloc(void** p, int64_t bytes);
 int b2bfs_host_free(void* p);
