@@ -114,6 +114,7 @@ static BfsParams make_params(const b2bfs* h) {
   p.g.rowptr = h->csr.rowptr;
   p.g.col = h->csr.col;
   p.g.visited_init = h->csr.visited_init;
+  p.g.first_nbr = h->csr.first_nbr;
   p.s = h->sv;
   p.tn.mode = h->mode;
   p.tn.alpha = h->alpha;

@@ -169,6 +169,7 @@ __device__ __forceinline__ void phase_init(const BfsParams& p, int64_t src) {
       c->slot[k].wide_count = 0;
       c->slot[k].edges = 0;
       c->slot[k].bu_count = 0;
+      c->slot[k].bu_cursor = 0;
     }
     const int64_t deg = p.g.rowptr[src + 1] - p.g.rowptr[src];
     if (deg < kNarrow) {
@@ -260,7 +261,7 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
   if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
   if (bid == 0 && threadIdx.x == 0) {  // recycle the slot two levels ahead
     LevelSlot* z = &p.s.ctl->slot[(level + 2) & 3];
-    z->q_count = 0; z->wide_count = 0; z->edges = 0; z->bu_count = 0;
+    z->q_count = 0; z->wide_count = 0; z->edges = 0; z->bu_count = 0; z->bu_cursor = 0;
   }
   __syncwarp();
 
@@ -331,40 +332,52 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
 }
 
 // ---------------------------------------------------------------------------------------------
-// bottom-up.  One visited-bitmap WORD PER LANE: a warp reads 32 words with one coalesced load and
-// every lane walks the unvisited vertices of its own word, so all 32 lanes stay busy whether 60 %
-// (first bottom-up level) or 1 % (later levels) of the vertices are unvisited.  The walk is a
-// four-stage software pipeline — per round a lane (A) requests the row extent of its next vertex,
-// (B) requests the first kBuFirst neighbour ids of the vertex from the round before, (C) requests
-// the frontier-bitmap words for the neighbours loaded the round before that, and (D) looks at the
-// answers of the round before that — so no round waits on a load it issued itself: the
-// rowptr -> col -> bitmap chain (2 DRAM + 1 L2 latency) overlaps across consecutive vertices.
-// Vertices not settled by their first kBuFirst neighbours go to a per-warp list in shared memory
-// and are finished four at a time by 8-lane groups with coalesced 32-byte reads and early exit.
-// Next-frontier and visited words are written once, by the lane that owns them, coalesced.
-// algorithmic bytes per level: n/8 (visited) + n/8 (next) + 16 B per unvisited vertex (row extent)
-// + 4 B per neighbour entry inspected + 8 B per discovered vertex; frontier probes hit L1/L2.
+// bottom-up, in three tiers of decreasing population and increasing cost per vertex.
+//   tier 1  one lane per VERTEX of a visited-bitmap word that still has unvisited bits: read
+//           first_nbr[v] (coalesced, 4 B per vertex, no rowptr/col access) and probe the frontier
+//           bitmap.  In a power-law graph the lowest-id neighbour is usually a hub, so most of the
+//           first bottom-up level ends here.  Software-pipelined over the words of a 32-word batch
+//           (load for word j+2, probe for word j+1, evaluate word j).  Batches are claimed from an
+//           atomic cursor, so warps that draw sparse regions simply take more batches.
+//   tier 2  misses are compacted into a per-warp list in shared memory and taken 32 at a time, one
+//           lane per vertex: row extent -> neighbours 2..5 -> four probes, as a four-stage pipeline
+//           across rounds, so the rowptr -> col -> bitmap chain of one vertex overlaps its
+//           neighbours' in the list.
+//   tier 3  rows still unresolved after five neighbours: 8 lanes per vertex, 32-byte reads, early exit.
+// The warp that owns a batch clears its next-frontier words first; all finds are then OR-ed into the
+// next-frontier and visited words (one atomic per word in tier 1, per vertex in tiers 2 and 3 —
+// distinct addresses, no hot line).
+// algorithmic bytes per level: n/8 (visited) + n/8 (next) + 4 B per unvisited vertex (first_nbr)
+// + 16 B row extent and 4 B per further neighbour inspected for tier-2/3 vertices + 8 B per
+// discovered vertex; frontier probes hit L1/L2.
 // ---------------------------------------------------------------------------------------------
-constexpr int kBuFirst = 2;      // neighbours probed in the pipelined pass
-constexpr int kBuDeferFlush = kStageCap - 32;
+constexpr int kBuT2 = 4;                       // neighbours 2..5 are probed in tier 2
+constexpr int kT2Cap = 2 * kStageCap;          // WarpStage::narrow + ::wide, contiguous
+constexpr int kT3Cap = kStageCap;              // WarpStage::witems
 
-// finish the listed vertices: 8 lanes per vertex, 8 entries per step
-__device__ __forceinline__ void bu_finish_deferred(const BfsParams& p, int level, const uint32_t* fr, WarpStage& sg,
-                                                   int64_t w0, unsigned long long& edges_acc) {
+__device__ __forceinline__ void bu_found(const BfsParams& p, int level, uint32_t* nx, int32_t v, int32_t par) {
+  p.s.depth[v] = level + 1;
+  p.s.parent[v] = par;
+  atomicOr(&nx[(uint32_t)v >> 5], 1u << (v & 31));
+  atomicOr(&p.s.visited[(uint32_t)v >> 5], 1u << (v & 31));
+}
+
+// tier 3: finish the listed vertices from their 6th neighbour on, 8 lanes per vertex
+__device__ __forceinline__ void bu_tier3(const BfsParams& p, int level, const uint32_t* fr, uint32_t* nx,
+                                         int32_t* list, int* cnt_p, unsigned long long& count_acc) {
   __syncwarp();
   const unsigned lane = lane_id();
-  const int cnt = *reinterpret_cast<volatile int*>(&sg.ncnt);
+  const int cnt = *reinterpret_cast<volatile int*>(cnt_p);
   const int g = lane >> 3, gl = lane & 7;
   for (int base = 0; base < cnt; base += 4) {
     const int idx = base + g;
     const bool has = idx < cnt;
-    const int32_t v = has ? sg.narrow[idx] : 0;
-    int64_t r0 = 0, re = 0;
+    const int32_t v = has ? list[idx] : 0;
+    int64_t pos = 0, re = 0;
     if (has) {
-      r0 = __ldg(p.g.rowptr + v);
+      pos = __ldg(p.g.rowptr + v) + 1 + kBuT2;
       re = __ldg(p.g.rowptr + v + 1);
     }
-    int64_t pos = r0 + kBuFirst;
     bool active = has && pos < re;
     int32_t par = -1;
     while (__ballot_sync(0xffffffffu, active)) {
@@ -385,11 +398,77 @@ __device__ __forceinline__ void bu_finish_deferred(const BfsParams& p, int level
       }
     }
     if (has && gl == 0 && par >= 0) {
-      p.s.depth[v] = level + 1;
-      p.s.parent[v] = par;
-      atomicOr(reinterpret_cast<unsigned int*>(&sg.wide[((int64_t)v >> 5) - w0]), 1u << (v & 31));
-      edges_acc += (unsigned long long)(re - r0);
+      bu_found(p, level, nx, v, par);
+      count_acc++;
     }
+  }
+  __syncwarp();
+  if (lane == 0) *cnt_p = 0;
+  __syncwarp();
+}
+
+// tier 2: listed vertices, one per lane, 4-stage pipeline across rounds of 32
+__device__ __forceinline__ void bu_tier2(const BfsParams& p, int level, const uint32_t* fr, uint32_t* nx,
+                                         WarpStage& sg, unsigned long long& count_acc) {
+  __syncwarp();
+  const unsigned lane = lane_id();
+  int32_t* list = sg.narrow;  // kT2Cap entries (narrow + wide)
+  const int cnt = *reinterpret_cast<volatile int*>(&sg.ncnt);
+  const int rounds = (cnt + 31) >> 5;
+  int32_t vA = -1, vB = -1, vC = -1;
+  int64_t rsA = 0, reA = 0;
+  int nB = 0, nC = 0;  // neighbours 2..5 actually present
+  bool moreB = false, moreC = false;
+  int32_t uB[kBuT2], uC[kBuT2];
+  uint32_t pw[kBuT2];
+#pragma unroll
+  for (int k = 0; k < kBuT2; ++k) { uB[k] = 0; uC[k] = 0; pw[k] = 0; }
+  for (int r = 0; r < rounds + 3; ++r) {
+    // D: evaluate
+    if (vC >= 0) {
+      int32_t par = -1;
+#pragma unroll
+      for (int k = kBuT2 - 1; k >= 0; --k)
+        if (k < nC && ((pw[k] >> (uC[k] & 31)) & 1u)) par = uC[k];
+      if (par >= 0) {
+        bu_found(p, level, nx, vC, par);
+        count_acc++;
+      } else if (moreC) {
+        sg.witems[atomicAdd(&sg.wcnt, 1)] = vC;
+      }
+    }
+    // C: probes for the neighbours that arrived
+    vC = vB; nC = nB; moreC = moreB;
+#pragma unroll
+    for (int k = 0; k < kBuT2; ++k) uC[k] = uB[k];
+    if (vC >= 0) {
+#pragma unroll
+      for (int k = 0; k < kBuT2; ++k) pw[k] = fr[(uint32_t)uC[k] >> 5];
+    }
+    // B: neighbours 2..5 of the row whose extent arrived
+    vB = vA;
+    if (vB >= 0) {
+      const int64_t d = reA - rsA;
+      nB = (int)min((int64_t)kBuT2, d - 1);
+      moreB = d > 1 + kBuT2;
+      if (nB <= 0) {
+        vB = -1;  // degree 1: its only neighbour was probed in tier 1
+      } else {
+#pragma unroll
+        for (int k = 0; k < kBuT2; ++k) uB[k] = __ldg(p.g.col + rsA + 1 + (k < nB ? k : 0));
+      }
+    }
+    // A: next list entry
+    const int i = r * 32 + (int)lane;
+    if (r < rounds && i < cnt) {
+      vA = list[i];
+      rsA = __ldg(p.g.rowptr + vA);
+      reA = __ldg(p.g.rowptr + vA + 1);
+    } else {
+      vA = -1;
+    }
+    __syncwarp();
+    if (*reinterpret_cast<volatile int*>(&sg.wcnt) > kT3Cap - 32) bu_tier3(p, level, fr, nx, sg.witems, &sg.wcnt, count_acc);
   }
   __syncwarp();
   if (lane == 0) sg.ncnt = 0;
@@ -402,80 +481,81 @@ __device__ __forceinline__ void phase_bottom_up(const BfsParams& p, const LoopSt
   uint32_t* nx = p.s.bitmap[st.fb ^ 1];
   LevelSlot* ns = &p.s.ctl->slot[(level + 1) & 3];
   const unsigned lane = lane_id();
-  WarpStage& sg = stage[threadIdx.x >> 5];  // narrow[] = deferred list, wide[0..31] = found bits per word
-  const int64_t gw = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-  const int64_t nwarps = (int64_t)gridDim.x * kWarpsPerBlock;
-  unsigned long long edges_acc = 0, count_acc = 0;
+  WarpStage& sg = stage[threadIdx.x >> 5];
+  unsigned long long count_acc = 0;
 
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     LevelSlot* z = &p.s.ctl->slot[(level + 2) & 3];
-    z->q_count = 0; z->wide_count = 0; z->edges = 0; z->bu_count = 0;
+    z->q_count = 0; z->wide_count = 0; z->edges = 0; z->bu_count = 0; z->bu_cursor = 0;
   }
-  if (lane == 0) sg.ncnt = 0;
-  sg.wide[lane] = 0;
+  if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
   __syncwarp();
+  int t2n = 0;  // warp-uniform mirror of sg.ncnt while tier 1 appends
 
-  for (int64_t w0 = gw * 32; w0 < p.g.nwords; w0 += nwarps * 32) {
+  for (;;) {
+    unsigned long long w0u = 0;
+    if (lane == 0) w0u = atomicAdd(&ns->bu_cursor, 32ull);
+    const int64_t w0 = (int64_t)__shfl_sync(0xffffffffu, w0u, 0);
+    if (w0 >= p.g.nwords) break;
     const int64_t w = w0 + lane;
     const bool inr = w < p.g.nwords;
     const uint32_t vis = inr ? p.s.visited[w] : 0xffffffffu;
-    uint32_t todo = ~vis, found_bits = 0;
-    int bA = -1, bB = -1, bC = -1;
-    int64_t rsA = 0, reA = 0, rsB = 0, nC = 0;
-    int64_t nB = 0;
-    int32_t uB0 = 0, uB1 = 0, uC0 = 0, uC1 = 0;
-    uint32_t pw0 = 0, pw1 = 0;
-    while (__ballot_sync(0xffffffffu, (todo != 0) | (bA >= 0) | (bB >= 0) | (bC >= 0))) {
-      // D: answers for the vertex probed last round
-      if (bC >= 0) {
-        const bool h0 = (pw0 >> (uC0 & 31)) & 1u;
-        const bool h1 = nC > 1 && ((pw1 >> (uC1 & 31)) & 1u);
-        const int64_t v = w * 32 + bC;
-        if (h0 | h1) {
+    const uint32_t todo = ~vis;
+    uint32_t found_bits = 0;
+    // clear the stale word now; every find of this level is OR-ed in afterwards (tier 2 may run
+    // in the middle of a batch and must not be overwritten by a later whole-word store)
+    if (inr) nx[w] = 0;
+    unsigned words = __ballot_sync(0xffffffffu, todo != 0);
+    // tier 1, pipelined over the words of this batch that have unvisited vertices
+    int jA = -1, jB = -1;
+    bool myA = false, myB = false;
+    int32_t fA = 0, fB = 0;
+    uint32_t pwB = 0;
+    while (words || jA >= 0 || jB >= 0) {  // warp-uniform
+      // evaluate word jB
+      if (jB >= 0) {
+        const bool hit = myB && ((pwB >> (fB & 31)) & 1u);
+        const int64_t v = (w0 + jB) * 32 + lane;
+        if (hit) {
           p.s.depth[v] = level + 1;
-          p.s.parent[v] = h0 ? uC0 : uC1;
-          found_bits |= 1u << bC;
-          edges_acc += (unsigned long long)nC;
-        } else if (nC > kBuFirst) {
-          sg.narrow[atomicAdd(&sg.ncnt, 1)] = (int32_t)v;
+          p.s.parent[v] = fB;
         }
+        const unsigned fm = __ballot_sync(0xffffffffu, hit);
+        if ((int)lane == jB) found_bits |= fm;
+        const unsigned mm = __ballot_sync(0xffffffffu, myB && !hit);
+        if (myB && !hit) sg.narrow[t2n + __popc(mm & ((1u << lane) - 1u))] = (int32_t)v;
+        t2n += __popc(mm);
       }
-      // C: request frontier words for the neighbours that arrived
-      bC = bB; nC = nB; uC0 = uB0; uC1 = uB1;
-      if (bC >= 0) {
-        pw0 = fr[(uint32_t)uC0 >> 5];
-        pw1 = fr[(uint32_t)uC1 >> 5];
-      }
-      // B: request the first neighbours of the row whose extent arrived
-      bB = bA; rsB = rsA; nB = reA - rsA;
-      if (bB >= 0) {
-        uB0 = __ldg(p.g.col + rsB);
-        uB1 = __ldg(p.g.col + rsB + (nB > 1 ? 1 : 0));
-      }
-      // A: request the extent of the next unvisited vertex of this lane's word
-      if (todo) {
-        bA = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const int64_t v = w * 32 + bA;
-        rsA = __ldg(p.g.rowptr + v);
-        reA = __ldg(p.g.rowptr + v + 1);
+      // probe for word jA
+      jB = jA; myB = myA; fB = fA;
+      if (jB >= 0 && myB) pwB = fr[(uint32_t)fB >> 5];
+      // first neighbours of the next word with unvisited vertices
+      if (words) {
+        jA = __ffs(words) - 1;
+        words &= words - 1;
+        const uint32_t tw = __shfl_sync(0xffffffffu, todo, jA);
+        myA = (tw >> lane) & 1u;
+        fA = myA ? __ldg(p.g.first_nbr + (w0 + jA) * 32 + lane) : 0;
       } else {
-        bA = -1;
+        jA = -1;
       }
-      __syncwarp();
-      if (*reinterpret_cast<volatile int*>(&sg.ncnt) >= kBuDeferFlush) bu_finish_deferred(p, level, fr, sg, w0, edges_acc);
+      if (t2n > kT2Cap - 32) {
+        __syncwarp();
+        if (lane == 0) sg.ncnt = t2n;
+        bu_tier2(p, level, fr, nx, sg, count_acc);
+        t2n = 0;
+      }
     }
-    bu_finish_deferred(p, level, fr, sg, w0, edges_acc);
-    found_bits |= (uint32_t)sg.wide[lane];
-    sg.wide[lane] = 0;
-    if (inr) {
-      nx[w] = found_bits;
-      if (found_bits) p.s.visited[w] = vis | found_bits;
+    if (inr && found_bits) {
+      atomicOr(&nx[w], found_bits);
+      atomicOr(&p.s.visited[w], found_bits);
       count_acc += __popc(found_bits);
     }
     __syncwarp();
   }
-  block_accumulate(edges_acc, &ns->edges);
+  if (lane == 0) sg.ncnt = t2n;
+  bu_tier2(p, level, fr, nx, sg, count_acc);
+  bu_tier3(p, level, fr, nx, sg.witems, &sg.wcnt, count_acc);
   block_accumulate(count_acc, &ns->bu_count);
 }
 

@@ -15,6 +15,7 @@ struct BuiltCsr {
   int32_t* col = nullptr;           // entries (+64 padding ints)
   uint32_t* orig_deg = nullptr;     // nrows: the reference's edgesSize[]
   uint32_t* visited_init = nullptr; // nwords
+  int32_t* first_nbr = nullptr;     // nwords * 32
 };
 
 Status generate_edges_device(int kind, int scale, int ef, uint64_t seed, int64_t first, int64_t count, int32_t* src,

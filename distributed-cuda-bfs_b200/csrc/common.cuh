@@ -59,6 +59,7 @@ struct GraphView {
   const int64_t* rowptr;     // n+1 offsets into col
   const int32_t* col;        // neighbour ids, sorted ascending inside a row
   const uint32_t* visited_init;  // bit set = never scan this vertex bottom-up (degree 0, or id >= n)
+  const int32_t* first_nbr;      // col[rowptr[v]] (or -1): lets bottom-up probe one neighbour without touching rowptr/col
 };
 
 // Per-level counters.  Every field that many warps hit with atomics sits on its own 128-byte line
@@ -68,6 +69,7 @@ struct alignas(128) LevelSlot {
   alignas(128) unsigned int wide_count;       // tail of the wide-item next queue
   alignas(128) unsigned long long edges;      // sum of degrees of the vertices found this level
   alignas(128) unsigned long long bu_count;   // vertices found by a bottom-up level
+  alignas(128) unsigned long long bu_cursor;  // next unclaimed batch of bitmap words (dynamic balance)
 };
 
 struct SearchResult {

@@ -178,7 +178,9 @@ __global__ void __launch_bounds__(kBlock) finish_rows_kernel(int64_t nrows, int6
                                                              const int64_t* __restrict__ rowptr,
                                                              const int64_t* __restrict__ orig_rowptr,
                                                              uint32_t* __restrict__ orig_deg,
+                                                             const int32_t* __restrict__ col,
                                                              uint32_t* __restrict__ visited_init,
+                                                             int32_t* __restrict__ first_nbr,
                                                              unsigned long long* wide_items,
                                                              unsigned long long* max_degree) {
   const int lane = threadIdx.x & 31;
@@ -188,8 +190,10 @@ __global__ void __launch_bounds__(kBlock) finish_rows_kernel(int64_t nrows, int6
     const int64_t v = w * 32 + lane;
     bool skip = true;
     unsigned long long items = 0;
+    if (v >= nrows) first_nbr[v] = -1;
     if (v < nrows) {
       const int64_t d = rowptr[v + 1] - rowptr[v];
+      first_nbr[v] = d > 0 ? col[rowptr[v]] : -1;
       orig_deg[v] = (uint32_t)(orig_rowptr[v + 1] - orig_rowptr[v]);
       skip = d == 0;
       if (d >= kNarrow) items = (unsigned long long)((d + kChunk - 1) / kChunk);
@@ -286,6 +290,7 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   B2_CUDA(cudaMalloc(&out->col, ((size_t)entries + 64) * sizeof(int32_t)));
   B2_CUDA(cudaMalloc(&out->orig_deg, (size_t)(nrows > 0 ? nrows : 1) * sizeof(uint32_t)));
   B2_CUDA(cudaMalloc(&out->visited_init, (size_t)nwords * sizeof(uint32_t)));
+  B2_CUDA(cudaMalloc(&out->first_nbr, (size_t)nwords * 32 * sizeof(int32_t)));
   B2_CUDA(cudaMemsetAsync(out->col + entries, 0xff, 64 * sizeof(int32_t), stream));
   if (N == 0) {
     B2_CUDA(cudaMemsetAsync(out->rowptr, 0, (size_t)(nrows + 1) * sizeof(int64_t), stream));
@@ -297,8 +302,8 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   }
   const int64_t fblocks = (nwords + kWarpsPerBlock - 1) / kWarpsPerBlock;
   const int fgrid = (int)(fblocks < (int64_t)kSMs * 8 ? fblocks : (int64_t)kSMs * 8);
-  finish_rows_kernel<<<fgrid, kBlock, 0, stream>>>(nrows, nwords, out->rowptr, orig_rowptr, out->orig_deg,
-                                                   out->visited_init, counters + 1, counters + 2);
+  finish_rows_kernel<<<fgrid, kBlock, 0, stream>>>(nrows, nwords, out->rowptr, orig_rowptr, out->orig_deg, out->col,
+                                                   out->visited_init, out->first_nbr, counters + 1, counters + 2);
   if (launches) *launches += 1;
   unsigned long long hc[2] = {0, 0};
   B2_CUDA(cudaMemcpyAsync(hc, counters + 1, sizeof(hc), cudaMemcpyDeviceToHost, stream));
@@ -321,6 +326,7 @@ void free_csr(BuiltCsr* c) {
   cudaFree(c->col);
   cudaFree(c->orig_deg);
   cudaFree(c->visited_init);
+  cudaFree(c->first_nbr);
   *c = BuiltCsr();
 }
 
