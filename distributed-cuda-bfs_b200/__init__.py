@@ -210,8 +210,11 @@ class Bfs:
         self._check(lib().b2bfs_copy_edges(self._h, first, count, s.ctypes.data, d.ctypes.data))
         return s, d
 
-    def csr(self):
+    def csr(self, rowptr_only: bool = False):
         rowptr = np.empty(self.num_vertices + 1, np.int64)
+        if rowptr_only:
+            self._check(lib().b2bfs_copy_csr(self._h, rowptr.ctypes.data, None))
+            return rowptr
         col = np.empty(self.csr_entries, np.int32)
         self._check(lib().b2bfs_copy_csr(self._h, rowptr.ctypes.data, col.ctypes.data))
         return rowptr, col
