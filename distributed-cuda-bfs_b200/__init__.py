@@ -86,6 +86,8 @@ def lib() -> C.CDLL:
             "b2bfs_device_depth": ([vp, C.POINTER(vp)], C.c_int),
             "b2bfs_device_parent": ([vp, C.POINTER(vp)], C.c_int),
             "b2bfs_last_trace": ([vp, vp, vp, vp, C.c_int], C.c_int),
+            "b2bfs_search_noalloc": ([C.c_int, i64, i64, vp, vp, i64, vp, vp, vp, C.POINTER(C.c_int32)], C.c_int),
+            "b2bfs_noalloc_last_error": ([], C.c_char_p),
             "b2bfs_host_alloc": ([C.POINTER(vp), i64], C.c_int),
             "b2bfs_host_free": ([vp], C.c_int),
             "b2bfs_destroy": ([vp], C.c_int),
@@ -96,6 +98,21 @@ def lib() -> C.CDLL:
             fn.argtypes, fn.restype = args, res
         _lib = L
     return _lib
+
+
+NOALLOC_MAX_VERTICES = 262144
+NOALLOC_MAX_ENTRIES = 16777216
+
+
+def search_noalloc(device: int, n: int, entries: int, rowptr_ptr: int, col_ptr: int, src: int, depth_ptr: int,
+                   parent_ptr: int, stream_ptr: int | None = None) -> int:
+    """b2bfs_search_noalloc over raw DEVICE pointers (ints).  Returns the number of levels."""
+    levels = C.c_int32(0)
+    rc = lib().b2bfs_search_noalloc(device, n, entries, rowptr_ptr, col_ptr, src, depth_ptr, parent_ptr, stream_ptr,
+                                    C.byref(levels))
+    if rc:
+        raise B2BfsError(rc, lib().b2bfs_noalloc_last_error().decode())
+    return levels.value
 
 
 class PinnedArray:

@@ -137,6 +137,29 @@ int b2bfs_device_parent(const b2bfs_t* h, const int32_t** parent_dev);
  * (<= cap) or a negative error.  Stands in for the commented-out per-level printf at bfs.cu:576. */
 int b2bfs_last_trace(b2bfs_t* h, int32_t* level_out, int32_t* phase_out, double* us_out, int cap);
 
+/* One search with NO device allocation (no counterpart in the reference).
+ * For callers that must not allocate when they need a search: code running under another
+ * framework's memory pool, loops whose allocations all happened at start-up, processes in which a
+ * different allocator already owns the whole card.  The caller passes the graph as a CSR that is
+ * ALREADY in device memory (rowptr: n+1 int64; col: `entries` int32, 16-byte aligned, neighbour
+ * ids in [0,n)) and device buffers for the results (depth, parent: n int32 each, 16-byte aligned);
+ * all scratch — bitmaps, frontier work lists, counters — lives in one array compiled into the
+ * library (about 7.4 MiB per GPU, resident from load to exit).  Limits: n <= B2BFS_NOALLOC_MAX_VERTICES
+ * and entries <= B2BFS_NOALLOC_MAX_ENTRIES, otherwise B2BFS_ERR_RANGE.  Top-down only; results are
+ * the same as b2bfs_run's (depth INT_MAX / parent -1 = unreachable).  Blocks until the search is
+ * complete on `cuda_stream` (a cudaStream_t, or NULL for the default stream).
+ * The first call on a device resolves the array's device address (cudaGetSymbolAddress) and sizes
+ * the launch; make that call before starting any stream capture.  All calls of a process share the
+ * one array (it still holds the previous call's contents; the entry point clears what has to start
+ * at zero), so two searches overlapping on the GPU would corrupt each other: the library takes a
+ * host lock and returns only when the search is complete, which keeps its own calls apart. */
+#define B2BFS_NOALLOC_MAX_VERTICES 262144   /* 2^18 */
+#define B2BFS_NOALLOC_MAX_ENTRIES 16777216  /* 2^24 directed CSR entries */
+int b2bfs_search_noalloc(int device, int64_t n, int64_t entries, const int64_t* rowptr_dev, const int32_t* col_dev,
+                         int64_t src, int32_t* depth_dev, int32_t* parent_dev, void* cuda_stream,
+                         int32_t* levels_out);
+const char* b2bfs_noalloc_last_error(void);
+
 /* Page-locked host memory for callers that want the copies in b2bfs_run at full PCIe speed. */
 int b2bfs_host_alloc(void** p, int64_t bytes);
 int b2bfs_host_free(void* p);
