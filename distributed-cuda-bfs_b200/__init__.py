@@ -79,6 +79,7 @@ def lib() -> C.CDLL:
             "b2bfs_num_input_edges": ([vp, C.POINTER(i64)], C.c_int),
             "b2bfs_csr_entries": ([vp, C.POINTER(i64)], C.c_int),
             "b2bfs_copy_degrees": ([vp, i32p], C.c_int),
+            "b2bfs_copy_row_degrees": ([vp, i32p], C.c_int),
             "b2bfs_copy_edges": ([vp, i64, i64, i32p, i32p], C.c_int),
             "b2bfs_copy_csr": ([vp, vp, i32p], C.c_int),
             "b2bfs_run": ([vp, i64, i32p, i32p, C.POINTER(Stats)], C.c_int),
@@ -115,6 +116,15 @@ def search_noalloc(device: int, n: int, entries: int, rowptr_ptr: int, col_ptr: 
     return levels.value
 
 
+def comm_unique_id() -> bytes:
+    """128-byte NCCL unique id (call on rank 0, hand to every rank's Bfs(...))."""
+    buf = C.create_string_buffer(128)
+    rc = lib().b2bfs_comm_unique_id(C.cast(buf, C.c_void_p))
+    if rc:
+        raise B2BfsError(rc, lib().b2bfs_last_error(None).decode())
+    return buf.raw
+
+
 class PinnedArray:
     """n x dtype in page-locked host memory (b2bfs_host_alloc), exposed as a numpy view."""
 
@@ -142,9 +152,17 @@ class Bfs:
     """One handle = one GPU holding one graph.  Mirrors the reference's initCuda2 + runCudaQueueBfs
     pair (bfs.cu:308, 542): load a graph once, then `run(src)` any number of times."""
 
-    def __init__(self, device: int = 0, **options):
+    def __init__(self, device: int = 0, rank: int = 0, world: int = 1, nccl_id: bytes | None = None, **options):
+        """world > 1: one rank of a multi-GPU job (one process per GPU); `nccl_id` is the 128-byte
+        id from comm_unique_id() on rank 0, delivered to every rank over any side channel."""
         self._h = C.c_void_p()
-        rc = lib().b2bfs_create(C.byref(self._h), device)
+        self.rank, self.world = rank, world
+        if world > 1:
+            assert nccl_id is not None and len(nccl_id) == 128
+            buf = C.create_string_buffer(bytes(nccl_id), 128)
+            rc = lib().b2bfs_create_rank(C.byref(self._h), device, rank, world, C.cast(buf, C.c_void_p))
+        else:
+            rc = lib().b2bfs_create(C.byref(self._h), device)
         if rc:
             raise B2BfsError(rc, lib().b2bfs_last_error(None).decode())
         for k, v in options.items():
@@ -219,6 +237,12 @@ class Bfs:
         self._check(lib().b2bfs_copy_degrees(self._h, out.ctypes.data))
         return out
 
+    def row_degrees(self):
+        """Degree in the resident (deduplicated) CSR for all n vertices; collective when world > 1."""
+        out = np.empty(self.num_vertices, np.int32)
+        self._check(lib().b2bfs_copy_row_degrees(self._h, out.ctypes.data))
+        return out
+
     def edges(self, first: int = 0, count: int | None = None):
         if count is None:
             count = self.num_input_edges - first
@@ -228,7 +252,8 @@ class Bfs:
         return s, d
 
     def csr(self, rowptr_only: bool = False):
-        rowptr = np.empty(self.num_vertices + 1, np.int64)
+        rows = self.get_option("local_rows") if self.world > 1 else self.num_vertices
+        rowptr = np.empty(rows + 1, np.int64)
         if rowptr_only:
             self._check(lib().b2bfs_copy_csr(self._h, rowptr.ctypes.data, None))
             return rowptr

@@ -11,6 +11,7 @@
 #include "bfs.cuh"
 #include "build.cuh"
 #include "edge_file.hpp"
+#include "multi.cuh"
 
 using namespace b2;
 
@@ -22,7 +23,7 @@ struct b2bfs {
   std::string err;
   // options
   int dedup = 1, mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED;
-  int alpha = 14, beta = 24, keep_edges = 1;
+  int alpha = 14, beta = 24, keep_edges = 1, gather_parent = 1;
   // graph
   bool has_graph = false;
   int64_t n = 0, m = 0;
@@ -33,6 +34,13 @@ struct b2bfs {
   Control* pinned_ctl = nullptr;
   int grid = 0;
   int64_t build_launches = 0;
+  // multi-rank (world > 1): 1-D partition of the rows, NCCL communicator, exchange buffers
+  MultiContext mc;
+  int64_t part = 0, vbase = 0, nloc = 0;
+  uint32_t *gfrontier = nullptr, *seen = nullptr;
+  int2* send_buf = nullptr;
+  unsigned int* send_count = nullptr;
+  int32_t* gather_tmp = nullptr;  // world * part ints: allgather staging for depth / parent / degrees
 };
 
 static thread_local std::string g_create_error;
@@ -65,7 +73,22 @@ static void free_search_state(b2bfs* h) {
   h->sv = SearchView{};
 }
 
+static void free_multi_state(b2bfs* h) {
+  cudaFree(h->gfrontier);
+  cudaFree(h->seen);
+  cudaFree(h->send_buf);
+  cudaFree(h->send_count);
+  cudaFree(h->gather_tmp);
+  cudaFree(h->mc.recv_buf);
+  h->gfrontier = h->seen = nullptr;
+  h->send_buf = nullptr;
+  h->send_count = nullptr;
+  h->gather_tmp = nullptr;
+  h->mc.recv_buf = nullptr;
+}
+
 static void free_graph(b2bfs* h) {
+  free_multi_state(h);
   cudaFree(h->d_src);
   cudaFree(h->d_dst);
   h->d_src = h->d_dst = nullptr;
@@ -75,10 +98,28 @@ static void free_graph(b2bfs* h) {
   h->n = h->m = 0;
 }
 
-// edges are in d_src/d_dst: build the CSR and the per-search buffers
+#define API_NCCL(h, expr)                                                                          \
+  do {                                                                                             \
+    ncclResult_t _r = (expr);                                                                      \
+    if (_r != ncclSuccess)                                                                         \
+      return fail(h, B2BFS_ERR_COMM, std::string(#expr) + ": " + (h)->mc.nccl->GetErrorString(_r)); \
+  } while (0)
+
+// edges are in d_src/d_dst: build the CSR (this rank's rows) and the per-search buffers
 static int finish_load(b2bfs* h) {
-  Status s = build_csr_device(h->d_src, h->d_dst, h->m, h->n, 0, h->n, false, h->dedup, h->stream,
-                              &h->csr, &h->build_launches);
+  const bool multi = h->world > 1;
+  if (multi) {
+    // contiguous ranges of `part` rows; a multiple of 128 so that bitmap slices are whole 16-byte groups
+    h->part = ((h->n + h->world - 1) / h->world + 127) / 128 * 128;
+    h->vbase = std::min(h->n, (int64_t)h->rank * h->part);
+    h->nloc = std::min(h->n, (int64_t)(h->rank + 1) * h->part) - h->vbase;
+  } else {
+    h->part = 0;
+    h->vbase = 0;
+    h->nloc = h->n;
+  }
+  Status s = build_csr_device(h->d_src, h->d_dst, h->m, h->n, h->vbase, h->vbase + h->nloc, multi, h->dedup,
+                              multi ? h->part / 32 : 0, h->stream, &h->csr, &h->build_launches);
   if (!s.ok()) {
     free_graph(h);
     return fail(h, s);
@@ -88,21 +129,50 @@ static int finish_load(b2bfs* h) {
     cudaFree(h->d_dst);
     h->d_src = h->d_dst = nullptr;
   }
-  const int64_t n = h->n, nw = h->csr.nwords;
+  const int64_t rows = multi ? h->part : h->n, nw = h->csr.nwords;
   const size_t wide_cap = (size_t)h->csr.wide_items + 1;
-  API_CUDA(h, cudaMalloc(&h->sv.depth, (size_t)(n + 4) * sizeof(int32_t)));
-  API_CUDA(h, cudaMalloc(&h->sv.parent, (size_t)(n + 4) * sizeof(int32_t)));
+  API_CUDA(h, cudaMalloc(&h->sv.depth, (size_t)(rows + 4) * sizeof(int32_t)));
+  API_CUDA(h, cudaMalloc(&h->sv.parent, (size_t)(rows + 4) * sizeof(int32_t)));
   API_CUDA(h, cudaMalloc(&h->sv.visited, (size_t)nw * sizeof(uint32_t)));
   API_CUDA(h, cudaMalloc(&h->sv.bitmap[0], (size_t)nw * sizeof(uint32_t)));
   API_CUDA(h, cudaMalloc(&h->sv.bitmap[1], (size_t)nw * sizeof(uint32_t)));
-  API_CUDA(h, cudaMalloc(&h->sv.queue[0], (size_t)n * sizeof(int32_t)));
-  API_CUDA(h, cudaMalloc(&h->sv.queue[1], (size_t)n * sizeof(int32_t)));
+  API_CUDA(h, cudaMalloc(&h->sv.queue[0], (size_t)(rows > 0 ? rows : 1) * sizeof(int32_t)));
+  API_CUDA(h, cudaMalloc(&h->sv.queue[1], (size_t)(rows > 0 ? rows : 1) * sizeof(int32_t)));
   API_CUDA(h, cudaMalloc(&h->sv.wideq[0], wide_cap * sizeof(int2)));
   API_CUDA(h, cudaMalloc(&h->sv.wideq[1], wide_cap * sizeof(int2)));
   API_CUDA(h, cudaMalloc(&h->sv.ctl, sizeof(Control)));
   API_CUDA(h, cudaMemsetAsync(h->sv.ctl, 0, sizeof(Control), h->stream));
+  if (multi) {
+    const size_t k = (size_t)h->world, part = (size_t)h->part;
+    API_CUDA(h, cudaMalloc(&h->gfrontier, k * part / 8));
+    API_CUDA(h, cudaMalloc(&h->seen, k * part / 8));
+    API_CUDA(h, cudaMalloc(&h->send_buf, k * part * sizeof(int2)));
+    API_CUDA(h, cudaMalloc(&h->send_count, k * 32 * sizeof(unsigned int)));
+    API_CUDA(h, cudaMalloc(&h->gather_tmp, k * part * sizeof(int32_t)));
+    API_CUDA(h, cudaMalloc(&h->mc.recv_buf, (k - 1) * part * sizeof(int2)));
+    API_CUDA(h, cudaMemsetAsync(h->sv.depth, 0xff, (size_t)(rows + 4) * sizeof(int32_t), h->stream));
+    // resident entries over all ranks (the switch heuristic's m_u starts from it)
+    unsigned long long e = (unsigned long long)h->csr.entries;
+    API_CUDA(h, cudaMemcpyAsync(h->mc.stats_send, &e, sizeof(e), cudaMemcpyHostToDevice, h->stream));
+    API_NCCL(h, h->mc.nccl->AllReduce(h->mc.stats_send, h->mc.stats_all, 1, ncclUint64, ncclSum, h->mc.comm, h->stream));
+    API_CUDA(h, cudaMemcpyAsync(h->mc.stats_host, h->mc.stats_all, sizeof(e), cudaMemcpyDeviceToHost, h->stream));
+    API_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->mc.entries_global = (int64_t)h->mc.stats_host[0];
+    h->mc.n_global = h->n;
+  }
   API_CUDA(h, cudaStreamSynchronize(h->stream));
   h->has_graph = true;
+  return B2BFS_OK;
+}
+
+// multi-rank: allgather one int32 per vertex (padded slices of `part`) and copy the first n to the host
+static int gather_i32(b2bfs* h, const int32_t* local_dev, int32_t* host_out, int64_t* d2h) {
+  API_NCCL(h, h->mc.nccl->AllGather(local_dev, h->gather_tmp, (size_t)h->part, ncclInt32, h->mc.comm, h->stream));
+  if (host_out) {
+    API_CUDA(h, cudaMemcpyAsync(host_out, h->gather_tmp, (size_t)h->n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    if (d2h) *d2h += h->n * (int64_t)sizeof(int32_t);
+    API_CUDA(h, cudaStreamSynchronize(h->stream));  // gather_tmp is reused by the next gather
+  }
   return B2BFS_OK;
 }
 
@@ -115,7 +185,18 @@ static BfsParams make_params(const b2bfs* h) {
   p.g.col = h->csr.col;
   p.g.visited_init = h->csr.visited_init;
   p.g.first_nbr = h->csr.first_nbr;
+  const bool multi = h->world > 1;
+  p.g.n = multi ? h->nloc : h->n;
+  p.g.vbase = h->vbase;
+  p.g.part = multi ? h->part : h->csr.nwords * 32;
+  p.g.rank = h->rank;
+  p.g.world = h->world;
   p.s = h->sv;
+  p.s.gfrontier = h->gfrontier;
+  p.s.seen = h->seen;
+  p.s.send_buf = h->send_buf;
+  p.s.send_count = h->send_count;
+  p.s.send_cap = h->part;
   p.tn.mode = h->mode;
   p.tn.alpha = h->alpha;
   p.tn.beta = h->beta;
@@ -153,14 +234,51 @@ int b2bfs_create(b2bfs_t** out, int device) {
 }
 
 int b2bfs_comm_unique_id(void* out128) {
-  (void)out128;
-  return fail(nullptr, B2BFS_ERR_UNSUPPORTED, "multi-rank support is not built into this library yet");
+  if (!out128) return fail(nullptr, B2BFS_ERR_ARG, "b2bfs_comm_unique_id: null buffer");
+  const char* err = nullptr;
+  const NcclApi* nccl = nccl_api(&err);
+  if (!nccl) return fail(nullptr, B2BFS_ERR_COMM, err);
+  static_assert(sizeof(ncclUniqueId) == 128, "the ABI promises a 128-byte id");
+  ncclUniqueId id;
+  const ncclResult_t r = nccl->GetUniqueId(&id);
+  if (r != ncclSuccess) return fail(nullptr, B2BFS_ERR_COMM, std::string("ncclGetUniqueId: ") + nccl->GetErrorString(r));
+  memcpy(out128, &id, sizeof(id));
+  return B2BFS_OK;
 }
 
 int b2bfs_create_rank(b2bfs_t** out, int device, int rank, int world, const void* nccl_id) {
-  (void)nccl_id;
   if (world == 1 && rank == 0) return b2bfs_create(out, device);
-  return fail(nullptr, B2BFS_ERR_UNSUPPORTED, "multi-rank support is not built into this library yet");
+  if (!out || !nccl_id || world < 2 || world > 8 || rank < 0 || rank >= world)
+    return fail(nullptr, B2BFS_ERR_ARG, "b2bfs_create_rank: need 2 <= world <= 8, 0 <= rank < world and a unique id");
+  const char* err = nullptr;
+  const NcclApi* nccl = nccl_api(&err);
+  if (!nccl) return fail(nullptr, B2BFS_ERR_COMM, err);
+  int rc = b2bfs_create(out, device);
+  if (rc) return rc;
+  b2bfs* h = *out;
+  h->rank = rank;
+  h->world = world;
+  h->mc.nccl = nccl;
+  h->mc.rank = rank;
+  h->mc.world = world;
+  ncclUniqueId id;
+  memcpy(&id, nccl_id, sizeof(id));
+  const ncclResult_t r = nccl->CommInitRank(&h->mc.comm, world, id, rank);
+  if (r != ncclSuccess) {
+    const std::string msg = std::string("ncclCommInitRank: ") + nccl->GetErrorString(r);
+    b2bfs_destroy(h);
+    *out = nullptr;
+    return fail(nullptr, B2BFS_ERR_COMM, msg);
+  }
+  cudaError_t e = cudaMalloc(&h->mc.stats_send, 16 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMalloc(&h->mc.stats_all, (size_t)world * 16 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMallocHost(&h->mc.stats_host, (size_t)world * 16 * sizeof(unsigned long long));
+  if (e != cudaSuccess) {
+    b2bfs_destroy(h);
+    *out = nullptr;
+    return fail(nullptr, B2BFS_ERR_NOMEM, "cannot allocate the per-level exchange records");
+  }
+  return B2BFS_OK;
 }
 
 int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
@@ -172,6 +290,7 @@ int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
   else if (k == "keep_edges" && (value == 0 || value == 1)) h->keep_edges = (int)value;
   else if (k == "mode" && (value == B2BFS_MODE_DIRECTION_OPT || value == B2BFS_MODE_TOP_DOWN)) h->mode = (int)value;
   else if (k == "engine" && (value == B2BFS_ENGINE_FUSED || value == B2BFS_ENGINE_STEPWISE)) h->engine = (int)value;
+  else if (k == "gather_parent" && (value == 0 || value == 1)) h->gather_parent = (int)value;
   else if (k == "alpha" && value >= 1 && value <= (1 << 20)) h->alpha = (int)value;
   else if (k == "beta" && value >= 1 && value <= (1 << 20)) h->beta = (int)value;
   else return fail(h, B2BFS_ERR_ARG, "unknown option or value out of range: " + k);
@@ -188,6 +307,11 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   else if (k == "alpha") *value = h->alpha;
   else if (k == "beta") *value = h->beta;
   else if (k == "grid") *value = h->grid;
+  else if (k == "gather_parent") *value = h->gather_parent;
+  else if (k == "rank") *value = h->rank;
+  else if (k == "world") *value = h->world;
+  else if (k == "local_rows") *value = h->nloc;
+  else if (k == "part") *value = h->part;
   else if (k == "wide_items") *value = h->csr.wide_items;
   else if (k == "max_degree") *value = h->csr.max_degree;
   else if (k == "build_launches") *value = h->build_launches;
@@ -283,8 +407,32 @@ int b2bfs_copy_degrees(b2bfs_t* h, int32_t* deg_out) {
   if (!h || !deg_out) return fail(h, B2BFS_ERR_ARG, "null argument");
   if (!h->has_graph) return fail(h, B2BFS_ERR_STATE, "no graph resident");
   API_CUDA(h, cudaSetDevice(h->device));
+  if (h->world > 1)  // collective: the reference's edgesSize[] for all n vertices, on every rank that asks
+    return gather_i32(h, reinterpret_cast<const int32_t*>(h->csr.orig_deg), deg_out, nullptr);
   API_CUDA(h, cudaMemcpy(deg_out, h->csr.orig_deg, (size_t)h->n * sizeof(int32_t), cudaMemcpyDeviceToHost));
   return B2BFS_OK;
+}
+
+int b2bfs_copy_row_degrees(b2bfs_t* h, int32_t* deg_out) {
+  if (!h) return fail(h, B2BFS_ERR_ARG, "null argument");
+  if (!h->has_graph) return fail(h, B2BFS_ERR_STATE, "no graph resident");
+  API_CUDA(h, cudaSetDevice(h->device));
+  if (h->world > 1) {
+    int32_t* mine = h->gather_tmp + (int64_t)h->rank * h->part;  // in-place allgather: own slice first
+    API_CUDA(h, cudaMemsetAsync(mine, 0, (size_t)h->part * sizeof(int32_t), h->stream));
+    Status s = row_degrees_device(h->csr.rowptr, h->nloc, mine, h->stream);
+    if (!s.ok()) return fail(h, s);
+    return gather_i32(h, mine, deg_out, nullptr);
+  }
+  if (!deg_out) return fail(h, B2BFS_ERR_ARG, "null argument");
+  int32_t* tmp = nullptr;
+  API_CUDA(h, cudaMalloc(&tmp, (size_t)h->n * sizeof(int32_t)));
+  Status s = row_degrees_device(h->csr.rowptr, h->n, tmp, h->stream);
+  if (s.ok() && cudaMemcpyAsync(deg_out, tmp, (size_t)h->n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess)
+    s = make_error(B2BFS_ERR_CUDA, "copy of row degrees failed");
+  cudaStreamSynchronize(h->stream);
+  cudaFree(tmp);
+  return s.ok() ? B2BFS_OK : fail(h, s);
 }
 
 int b2bfs_copy_edges(b2bfs_t* h, int64_t first, int64_t count, int32_t* src_out, int32_t* dst_out) {
@@ -301,37 +449,57 @@ int b2bfs_copy_csr(b2bfs_t* h, int64_t* rowptr_out, int32_t* col_out) {
   if (!h || !rowptr_out) return fail(h, B2BFS_ERR_ARG, "null argument");
   if (!h->has_graph) return fail(h, B2BFS_ERR_STATE, "no graph resident");
   API_CUDA(h, cudaSetDevice(h->device));
-  API_CUDA(h, cudaMemcpy(rowptr_out, h->csr.rowptr, (size_t)(h->n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  // multi-rank: this rank's rows only (local_rows + 1 offsets; col holds global ids)
+  API_CUDA(h, cudaMemcpy(rowptr_out, h->csr.rowptr, (size_t)(h->nloc + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost));
   if (col_out && h->csr.entries > 0)
     API_CUDA(h, cudaMemcpy(col_out, h->csr.col, (size_t)h->csr.entries * sizeof(int32_t), cudaMemcpyDeviceToHost));
   return B2BFS_OK;
 }
 
-static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent_out, b2bfs_stats* stats) {
+static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent_out, b2bfs_stats* stats,
+                    bool gather) {
   if (!h) return fail(h, B2BFS_ERR_ARG, "null handle");
   if (!h->has_graph) return fail(h, B2BFS_ERR_STATE, "b2bfs_run: no graph resident");
   if (src < 0 || src >= h->n) return fail(h, B2BFS_ERR_ARG, "b2bfs_run: source vertex outside [0, vertex_num)");
   const auto t0 = std::chrono::steady_clock::now();
   API_CUDA(h, cudaSetDevice(h->device));
   const BfsParams p = make_params(h);
+  const bool multi = h->world > 1;
   int64_t launches = 0;
+  MultiResult mr;
   API_CUDA(h, cudaEventRecord(h->ev0, h->stream));
-  Status s = (h->engine == B2BFS_ENGINE_FUSED) ? run_fused(p, src, h->grid, h->stream, &launches)
-                                                : run_stepwise(p, src, h->grid, h->stream, h->pinned_ctl, &launches);
+  Status s = multi ? run_multi(p, h->mc, src, h->grid, h->stream, &mr)
+           : (h->engine == B2BFS_ENGINE_FUSED) ? run_fused(p, src, h->grid, h->stream, &launches)
+                                               : run_stepwise(p, src, h->grid, h->stream, h->pinned_ctl, &launches);
   if (!s.ok()) return fail(h, s);
   API_CUDA(h, cudaEventRecord(h->ev1, h->stream));
   int64_t d2h = 0;
-  if (depth_out) {
-    API_CUDA(h, cudaMemcpyAsync(depth_out, h->sv.depth, (size_t)h->n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
-    d2h += h->n * (int64_t)sizeof(int32_t);
-  }
-  if (parent_out) {
-    API_CUDA(h, cudaMemcpyAsync(parent_out, h->sv.parent, (size_t)h->n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
-    d2h += h->n * (int64_t)sizeof(int32_t);
+  if (multi) {
+    launches = mr.launches;
+    if (gather) {  // collective: every rank takes part, whoever passed a buffer gets all n entries
+      int rc = gather_i32(h, h->sv.depth, depth_out, &d2h);
+      if (rc) return rc;
+      if (h->gather_parent) {
+        rc = gather_i32(h, h->sv.parent, parent_out, &d2h);
+        if (rc) return rc;
+      }
+    }
+  } else {
+    if (depth_out) {
+      API_CUDA(h, cudaMemcpyAsync(depth_out, h->sv.depth, (size_t)h->n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+      d2h += h->n * (int64_t)sizeof(int32_t);
+    }
+    if (parent_out) {
+      API_CUDA(h, cudaMemcpyAsync(parent_out, h->sv.parent, (size_t)h->n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+      d2h += h->n * (int64_t)sizeof(int32_t);
+    }
   }
   if (stats) {
     s = run_reach_stats(p, h->csr.orig_deg, h->stream, &launches);
     if (!s.ok()) return fail(h, s);
+    if (multi)
+      API_NCCL(h, h->mc.nccl->AllReduce(&h->sv.ctl->reached_vertices, &h->sv.ctl->reached_vertices, 2, ncclUint64, ncclSum,
+                                        h->mc.comm, h->stream));
     API_CUDA(h, cudaMemcpyAsync(h->pinned_ctl, h->sv.ctl, sizeof(Control), cudaMemcpyDeviceToHost, h->stream));
     d2h += (int64_t)sizeof(Control);
   }
@@ -341,14 +509,14 @@ static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent
     float ms = 0.f;
     API_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
     const Control* c = h->pinned_ctl;
-    stats->levels = c->result.levels;
-    stats->td_levels = c->result.td_levels;
-    stats->bu_levels = c->result.bu_levels;
+    stats->levels = multi ? mr.levels : c->result.levels;
+    stats->td_levels = multi ? mr.td_levels : c->result.td_levels;
+    stats->bu_levels = multi ? mr.bu_levels : c->result.bu_levels;
     stats->reserved0 = 0;
     stats->reached_vertices = (int64_t)c->reached_vertices;
     stats->reached_entries = (int64_t)c->reached_entries;
     stats->kernel_launches = launches;
-    stats->h2d_bytes = (h->engine == B2BFS_ENGINE_STEPWISE) ? (int64_t)sizeof(SearchResult) : 0;
+    stats->h2d_bytes = (!multi && h->engine == B2BFS_ENGINE_STEPWISE) ? (int64_t)sizeof(SearchResult) : 0;
     stats->d2h_bytes = d2h;
     stats->search_ms = ms;
     stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
@@ -357,11 +525,14 @@ static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent
 }
 
 int b2bfs_run(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent_out, b2bfs_stats* stats) {
-  if (h && !depth_out) return fail(h, B2BFS_ERR_ARG, "b2bfs_run: depth_out is null (use b2bfs_run_device to keep results in HBM)");
-  return run_impl(h, src, depth_out, parent_out, stats);
+  if (h && h->world == 1 && !depth_out)
+    return fail(h, B2BFS_ERR_ARG, "b2bfs_run: depth_out is null (use b2bfs_run_device to keep results in HBM)");
+  return run_impl(h, src, depth_out, parent_out, stats, true);
 }
 
-int b2bfs_run_device(b2bfs_t* h, int64_t src, b2bfs_stats* stats) { return run_impl(h, src, nullptr, nullptr, stats); }
+int b2bfs_run_device(b2bfs_t* h, int64_t src, b2bfs_stats* stats) {
+  return run_impl(h, src, nullptr, nullptr, stats, false);
+}
 
 int b2bfs_device_depth(const b2bfs_t* h, const int32_t** depth_dev) {
   if (!h || !depth_dev || !h->has_graph) return B2BFS_ERR_ARG;
@@ -399,6 +570,10 @@ int b2bfs_destroy(b2bfs_t* h) {
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
   free_graph(h);
+  if (h->mc.comm) h->mc.nccl->CommDestroy(h->mc.comm);
+  cudaFree(h->mc.stats_send);
+  cudaFree(h->mc.stats_all);
+  if (h->mc.stats_host) cudaFreeHost(h->mc.stats_host);
   if (h->pinned_ctl) cudaFreeHost(h->pinned_ctl);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);

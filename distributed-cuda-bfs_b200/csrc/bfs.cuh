@@ -14,6 +14,16 @@ Status search_grid_size(int device, int* grid_out);
 Status run_fused(const BfsParams& p, int64_t src, int grid, cudaStream_t stream, int64_t* launches);
 Status run_stepwise(const BfsParams& p, int64_t src, int grid, cudaStream_t stream, Control* pinned,
                     int64_t* launches);
+// launchers used by the multi-rank host loop (multi.cu)
+void launch_init(const BfsParams& p, int64_t src_local, int grid, cudaStream_t s);
+void launch_top_down_multi(const BfsParams& p, const LoopState& st, int grid, cudaStream_t s);
+void launch_apply_remote(const BfsParams& p, const LoopState& st, const int2* recv, int64_t count, int grid,
+                         cudaStream_t s);
+void launch_bottom_up(const BfsParams& p, const LoopState& st, int grid, cudaStream_t s);
+void launch_queue_to_bitmap(const BfsParams& p, const LoopState& st, int grid, cudaStream_t s);
+void launch_bitmap_to_queue(const BfsParams& p, const LoopState& st, int grid, cudaStream_t s);
+void launch_pack_stats(const BfsParams& p, int slot, unsigned long long* out, cudaStream_t s);
+
 Status run_reach_stats(const BfsParams& p, const uint32_t* orig_deg, cudaStream_t stream, int64_t* launches);
 
 }  // namespace b2

@@ -37,6 +37,13 @@ struct WarpStage {
   int ncnt, wcnt;
 };
 
+// Multi-rank top-down only: (vertex, parent) pairs whose vertex another rank owns, staged per warp and
+// drained into per-owner send buckets (one tail atomic per owner per 32 staged pairs).
+struct RemoteStage {
+  int2 pair[kStageCap];
+  int cnt;
+};
+
 // ---------------------------------------------------------------------------------------------
 // small helpers
 // ---------------------------------------------------------------------------------------------
@@ -134,12 +141,12 @@ __device__ __forceinline__ void phase_init(const BfsParams& p, int64_t src) {
     p4[i] = pnone;
     if ((src >> 2) == i) {  // same thread, program order: the seed lands after the fill
       p.s.depth[src] = 0;
-      p.s.parent[src] = (int32_t)src;
+      p.s.parent[src] = (int32_t)(src + p.g.vbase);
     }
   }
   for (int64_t i = (n4 << 2) + tid; i < n; i += nthreads) {
     p.s.depth[i] = (i == src) ? 0 : B2BFS_UNREACHED_DEPTH;
-    p.s.parent[i] = (i == src) ? (int32_t)src : -1;
+    p.s.parent[i] = (i == src) ? (int32_t)(src + p.g.vbase) : -1;
   }
   const int64_t w4 = p.g.nwords >> 2;
   const uint4* vi4 = reinterpret_cast<const uint4*>(p.g.visited_init);
@@ -171,8 +178,9 @@ __device__ __forceinline__ void phase_init(const BfsParams& p, int64_t src) {
       c->slot[k].bu_count = 0;
       c->slot[k].bu_cursor = 0;
     }
-    const int64_t deg = p.g.rowptr[src + 1] - p.g.rowptr[src];
-    if (deg < kNarrow) {
+    const int64_t deg = src >= 0 ? p.g.rowptr[src + 1] - p.g.rowptr[src] : 0;  // src < 0: another rank owns it
+    if (src < 0) {
+    } else if (deg < kNarrow) {
       p.s.queue[0][0] = (int32_t)src;
       c->slot[0].q_count = 1;
     } else {
@@ -213,39 +221,89 @@ __host__ __device__ inline LoopState initial_state(const BfsParams& p, int64_t s
 // algorithmic bytes per level: 4 B per frontier vertex / 8 B per item + 16 B row extent + 4 B per
 // neighbour entry; per discovered vertex 8 B (depth + parent) + 16 B its row extent + 4-8 B queue
 // ---------------------------------------------------------------------------------------------
+// Warp-uniform: drain staged remote pairs into the send bucket of each owner.
+__device__ __forceinline__ void remote_flush(const BfsParams& p, RemoteStage& rs, bool force) {
+  __syncwarp();
+  const unsigned lane = lane_id();
+  const int cnt = *reinterpret_cast<volatile int*>(&rs.cnt);
+  if (cnt < kStageFlush && !(force && cnt > 0)) return;
+  for (int i0 = 0; i0 < cnt; i0 += 32) {
+    const int i = i0 + (int)lane;
+    const bool has = i < cnt;
+    const int2 e = has ? rs.pair[i] : make_int2(0, 0);
+    const int owner = has ? (int)(e.x / p.g.part) : -1;
+    for (int d = 0; d < p.g.world; ++d) {
+      const unsigned m = __ballot_sync(0xffffffffu, owner == d);
+      if (!m) continue;
+      unsigned base = 0;
+      const int leader = __ffs(m) - 1;
+      if ((int)lane == leader) base = atomicAdd(&p.s.send_count[d * 32], (unsigned)__popc(m));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (owner == d) p.s.send_buf[(int64_t)d * p.s.send_cap + base + __popc(m & ((1u << lane) - 1u))] = e;
+    }
+  }
+  __syncwarp();
+  if (lane == 0) rs.cnt = 0;
+  __syncwarp();
+}
+
 // Four (u -> v) entries per lane at a time, phase by phase, so that the four visited probes, the
 // four claims and the four row-extent reads are each in flight together instead of forming one
-// long dependent chain per entry.
-__device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpStage& sg, const int32_t (&v)[4],
-                                          const int32_t (&u)[4], const bool (&valid)[4],
+// long dependent chain per entry.  v and u are GLOBAL ids; with kMulti a vertex another rank owns is
+// filtered through the `seen` bitmap and staged for its owner instead of being claimed here.
+template <bool kMulti>
+__device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpStage& sg, RemoteStage* rs,
+                                          const int32_t (&v)[4], const int32_t (&u)[4], const bool (&valid)[4],
                                           unsigned long long& edges_acc) {
   uint32_t word[4];
-  bool c[4];
+  bool c[4], local[4];
+  int32_t vl[4];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) word[k] = valid[k] ? p.s.visited[(uint32_t)v[k] >> 5] : 0xffffffffu;
+  for (int k = 0; k < 4; ++k) {
+    vl[k] = v[k] - (int32_t)p.g.vbase;
+    local[k] = !kMulti || (vl[k] >= 0 && vl[k] < (int32_t)p.g.n);
+  }
   // cheap read first; a stale "clear" only costs one extra atomic (bits only go 0 -> 1 in a search)
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t* bm = local[k] ? p.s.visited : p.s.seen;
+    const uint32_t idx = (uint32_t)(local[k] ? vl[k] : v[k]) >> 5;
+    word[k] = valid[k] ? bm[idx] : 0xffffffffu;
+  }
 #pragma unroll
   for (int k = 0; k < 4; ++k) c[k] = !((word[k] >> (v[k] & 31)) & 1u);
 #pragma unroll
-  for (int k = 0; k < 4; ++k)
-    if (c[k]) word[k] = atomicOr(&p.s.visited[(uint32_t)v[k] >> 5], 1u << (v[k] & 31));
+  for (int k = 0; k < 4; ++k) {
+    if (c[k]) {
+      uint32_t* bm = local[k] ? p.s.visited : p.s.seen;
+      const uint32_t idx = (uint32_t)(local[k] ? vl[k] : v[k]) >> 5;
+      word[k] = atomicOr(&bm[idx], 1u << (v[k] & 31));
+    }
+  }
 #pragma unroll
   for (int k = 0; k < 4; ++k) c[k] = c[k] && !((word[k] >> (v[k] & 31)) & 1u);
   int64_t d[4];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) d[k] = c[k] ? __ldg(p.g.rowptr + v[k] + 1) - __ldg(p.g.rowptr + v[k]) : 0;
+  for (int k = 0; k < 4; ++k)
+    d[k] = (c[k] && local[k]) ? __ldg(p.g.rowptr + vl[k] + 1) - __ldg(p.g.rowptr + vl[k]) : 0;
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     if (c[k]) {
-      p.s.depth[v[k]] = level + 1;
-      p.s.parent[v[k]] = u[k];
-      edges_acc += (unsigned long long)d[k];
-      route_vertex(sg, v[k], d[k]);
+      if (local[k]) {
+        p.s.depth[vl[k]] = level + 1;
+        p.s.parent[vl[k]] = u[k];
+        edges_acc += (unsigned long long)d[k];
+        route_vertex(sg, vl[k], d[k]);
+      } else if (kMulti) {
+        rs->pair[atomicAdd(&rs->cnt, 1)] = make_int2(v[k], u[k]);
+      }
     }
   }
 }
 
-__device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStage* stage, int bid, int nb) {
+template <bool kMulti>
+__device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStage* stage, int bid, int nb,
+                                               RemoteStage* rstage = nullptr) {
   const int level = st.level;
   const int32_t* q = p.s.queue[level & 1];
   const int2* wq = p.s.wideq[level & 1];
@@ -258,7 +316,10 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
   const int64_t nwarps = (int64_t)nb * kWarpsPerBlock;
   unsigned long long edges_acc = 0;
 
+  RemoteStage* rst = kMulti ? &rstage[threadIdx.x >> 5] : nullptr;
+  const int32_t vbase = (int32_t)p.g.vbase;
   if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
+  if (kMulti && lane == 0) rst->cnt = 0;
   if (bid == 0 && threadIdx.x == 0) {  // recycle the slot two levels ahead
     LevelSlot* z = &p.s.ctl->slot[(level + 2) & 3];
     z->q_count = 0; z->wide_count = 0; z->edges = 0; z->bu_count = 0; z->bu_cursor = 0;
@@ -300,12 +361,13 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
           }
           const uint32_t oe = __shfl_sync(0xffffffffu, excl, lo);
           const int64_t ors = __shfl_sync(0xffffffffu, rs, lo);
-          uu[j] = __shfl_sync(0xffffffffu, u, lo);
+          uu[j] = __shfl_sync(0xffffffffu, u, lo) + vbase;
           valid[j] = k < total;
           v[j] = valid[j] ? __ldg(p.g.col + ors + (k - oe)) : 0;
         }
-        td_visit4(p, level, sg, v, uu, valid, edges_acc);
+        td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc);
         stage_flush(sg, ns, nq, nwq, false);
+        if (kMulti) remote_flush(p, *rst, false);
       }
     } else {
       const int2 it = __ldcg(wq + (item - tiles));
@@ -318,14 +380,50 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
         if (base < re) {
           const int4 x = __ldg(reinterpret_cast<const int4*>(p.g.col + base));
           const int32_t v[4] = {x.x, x.y, x.z, x.w};
-          const int32_t uu[4] = {u, u, u, u};
+          const int32_t uu[4] = {u + vbase, u + vbase, u + vbase, u + vbase};
           const bool valid[4] = {base >= rs, base + 1 >= rs && base + 1 < re, base + 2 >= rs && base + 2 < re,
                                  base + 3 >= rs && base + 3 < re};
-          td_visit4(p, level, sg, v, uu, valid, edges_acc);
+          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc);
         }
         stage_flush(sg, ns, nq, nwq, false);
+        if (kMulti) remote_flush(p, *rst, false);
       }
     }
+  }
+  stage_flush(sg, ns, nq, nwq, true);
+  if (kMulti) remote_flush(p, *rst, true);
+  block_accumulate(edges_acc, &ns->edges);
+}
+
+// Multi-rank: claim the (vertex, parent) pairs other ranks discovered in this rank's rows and queue
+// the winners for the next level (same slot counters and staging as the local discoveries).
+__device__ __forceinline__ void phase_apply_remote(const BfsParams& p, const LoopState& st, WarpStage* stage,
+                                                   const int2* recv, int64_t count) {
+  const int level = st.level;
+  int32_t* nq = p.s.queue[(level + 1) & 1];
+  int2* nwq = p.s.wideq[(level + 1) & 1];
+  LevelSlot* ns = &p.s.ctl->slot[(level + 1) & 3];
+  WarpStage& sg = stage[threadIdx.x >> 5];
+  if (lane_id() == 0) { sg.ncnt = 0; sg.wcnt = 0; }
+  __syncwarp();
+  unsigned long long edges_acc = 0;
+  const int64_t nthreads = (int64_t)gridDim.x * kBlock;
+  const int64_t rounds = (count + nthreads - 1) / nthreads;
+  for (int64_t r = 0; r < rounds; ++r) {  // warp-uniform trip count
+    const int64_t i = r * nthreads + (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i < count) {
+      const int2 e = recv[i];
+      const int32_t vl = e.x - (int32_t)p.g.vbase;
+      const uint32_t w = (uint32_t)vl >> 5, bit = 1u << (vl & 31);
+      if (!(p.s.visited[w] & bit) && !(atomicOr(&p.s.visited[w], bit) & bit)) {
+        p.s.depth[vl] = level + 1;
+        p.s.parent[vl] = e.y;
+        const int64_t d = __ldg(p.g.rowptr + vl + 1) - __ldg(p.g.rowptr + vl);
+        edges_acc += (unsigned long long)d;
+        route_vertex(sg, vl, d);
+      }
+    }
+    stage_flush(sg, ns, nq, nwq, false);
   }
   stage_flush(sg, ns, nq, nwq, true);
   block_accumulate(edges_acc, &ns->edges);
@@ -477,7 +575,8 @@ __device__ __forceinline__ void bu_tier2(const BfsParams& p, int level, const ui
 
 __device__ __forceinline__ void phase_bottom_up(const BfsParams& p, const LoopState& st, WarpStage* stage) {
   const int level = st.level;
-  const uint32_t* fr = p.s.bitmap[st.fb];
+  // multi-rank: probe the allgathered frontier of all ranks (global ids), write this rank's slice
+  const uint32_t* fr = p.s.gfrontier ? p.s.gfrontier : p.s.bitmap[st.fb];
   uint32_t* nx = p.s.bitmap[st.fb ^ 1];
   LevelSlot* ns = &p.s.ctl->slot[(level + 1) & 3];
   const unsigned lane = lane_id();
@@ -625,7 +724,7 @@ __device__ __forceinline__ void phase_bitmap_to_queue(const BfsParams& p, const 
 __global__ void __launch_bounds__(kBlock) search_init_kernel(BfsParams p, int64_t src) { phase_init(p, src); }
 __global__ void __launch_bounds__(kBlock) top_down_kernel(BfsParams p, LoopState st) {
   __shared__ WarpStage stage[kWarpsPerBlock];
-  phase_top_down(p, st, stage, blockIdx.x, gridDim.x);
+  phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x);
 }
 __global__ void __launch_bounds__(kBlock) bottom_up_kernel(BfsParams p, LoopState st) {
   __shared__ WarpStage stage[kWarpsPerBlock];
@@ -637,6 +736,56 @@ __global__ void __launch_bounds__(kBlock) queue_to_bitmap_kernel(BfsParams p, Lo
 __global__ void __launch_bounds__(kBlock) bitmap_to_queue_kernel(BfsParams p, LoopState st) {
   __shared__ WarpStage stage[kWarpsPerBlock];
   phase_bitmap_to_queue(p, st, stage);
+}
+
+// ---------------------------------------------------------------------------------------------
+// multi-rank engine: the same phases, one launch each, with NCCL exchanges in between (multi.cu)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) top_down_multi_kernel(BfsParams p, LoopState st) {
+  __shared__ WarpStage stage[kWarpsPerBlock];
+  __shared__ RemoteStage rstage[kWarpsPerBlock];
+  phase_top_down<true>(p, st, stage, blockIdx.x, gridDim.x, rstage);
+}
+__global__ void __launch_bounds__(kBlock) apply_remote_kernel(BfsParams p, LoopState st, const int2* recv, int64_t count) {
+  __shared__ WarpStage stage[kWarpsPerBlock];
+  phase_apply_remote(p, st, stage, recv, count);
+}
+// one 16-word record per rank per exchange: [0] narrow queue tail, [1] wide tail, [2] degree sum,
+// [3] bottom-up finds, [4] source degree, [8 + d] pairs staged for rank d
+__global__ void pack_stats_kernel(BfsParams p, int slot, unsigned long long* out) {
+  const LevelSlot* s = &p.s.ctl->slot[slot & 3];
+  if (threadIdx.x == 0) {
+    out[0] = s->q_count;
+    out[1] = s->wide_count;
+    out[2] = s->edges;
+    out[3] = s->bu_count;
+    out[4] = (unsigned long long)p.s.ctl->src_degree;
+    out[5] = out[6] = out[7] = 0;
+  }
+  if (threadIdx.x < 8) out[8 + threadIdx.x] = (int)threadIdx.x < p.g.world ? p.s.send_count[threadIdx.x * 32] : 0;
+}
+
+void launch_init(const BfsParams& p, int64_t src_local, int grid, cudaStream_t s) {
+  search_init_kernel<<<grid, kBlock, 0, s>>>(p, src_local);
+}
+void launch_top_down_multi(const BfsParams& p, const LoopState& st, int grid, cudaStream_t s) {
+  top_down_multi_kernel<<<grid, kBlock, 0, s>>>(p, st);
+}
+void launch_apply_remote(const BfsParams& p, const LoopState& st, const int2* recv, int64_t count, int grid,
+                         cudaStream_t s) {
+  apply_remote_kernel<<<grid, kBlock, 0, s>>>(p, st, recv, count);
+}
+void launch_bottom_up(const BfsParams& p, const LoopState& st, int grid, cudaStream_t s) {
+  bottom_up_kernel<<<grid, kBlock, 0, s>>>(p, st);
+}
+void launch_queue_to_bitmap(const BfsParams& p, const LoopState& st, int grid, cudaStream_t s) {
+  queue_to_bitmap_kernel<<<grid, kBlock, 0, s>>>(p, st);
+}
+void launch_bitmap_to_queue(const BfsParams& p, const LoopState& st, int grid, cudaStream_t s) {
+  bitmap_to_queue_kernel<<<grid, kBlock, 0, s>>>(p, st);
+}
+void launch_pack_stats(const BfsParams& p, int slot, unsigned long long* out, cudaStream_t s) {
+  pack_stats_kernel<<<1, 32, 0, s>>>(p, slot, out);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -705,7 +854,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
       ++group_seq;
       if ((int)blockIdx.x < group) {
         do {
-          phase_top_down(p, st, stage, blockIdx.x, group);
+          phase_top_down<false>(p, st, stage, blockIdx.x, group);
           group_barrier(&p.s.ctl->group_barrier, epoch, group);
           const LevelSlot* ns = &p.s.ctl->slot[(st.level + 1) & 3];
           cv = advance(st, p.tn, p.g.n, ld_volatile(&ns->q_count), ld_volatile(&ns->wide_count),
@@ -735,7 +884,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
       trace_mark(p.s.ctl, ntrace, st.level, 5);
     } else {
       const int ph = st.mode == 0 ? 1 : 2;
-      if (st.mode == 0) phase_top_down(p, st, stage, blockIdx.x, gridDim.x); else phase_bottom_up(p, st, stage);
+      if (st.mode == 0) phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x); else phase_bottom_up(p, st, stage);
       grid.sync();
       trace_mark(p.s.ctl, ntrace, st.level, ph);
       const LevelSlot* ns = &p.s.ctl->slot[(st.level + 1) & 3];

@@ -53,9 +53,12 @@ inline Status make_error(int code, const std::string& msg) {
 // resident graph (this rank's rows) and per-search state, as the kernels see them
 // ---------------------------------------------------------------------------------------------
 struct GraphView {
-  int64_t n;                 // vertices (global)
+  int64_t n;                 // rows resident on this GPU (= all vertices on a single GPU)
   int64_t nwords;            // bitmap words covering n (multiple of 4)
   int64_t entries;           // resident CSR entries
+  int64_t vbase;             // global id of local row 0 (0 on a single GPU); col[] holds GLOBAL ids
+  int64_t part;              // rows per rank of the 1-D partition (multiple of 128); owner(v) = v / part
+  int rank, world;
   const int64_t* rowptr;     // n+1 offsets into col
   const int32_t* col;        // neighbour ids, sorted ascending inside a row
   const uint32_t* visited_init;  // bit set = never scan this vertex bottom-up (degree 0, or id >= n)
@@ -116,6 +119,12 @@ struct SearchView {
   int32_t* queue[2];         // narrow rows (degree < kNarrow): vertex ids, n each
   int2* wideq[2];            // wide rows: (vertex, chunk) work items of <= kChunk entries
   Control* ctl;
+  // multi-rank only (nullptr / 0 on a single GPU)
+  uint32_t* gfrontier;       // world * part bits: the frontier of ALL ranks (allgathered), probed bottom-up
+  uint32_t* seen;            // world * part bits: remote vertices this rank has already sent to their owner
+  int2* send_buf;            // world buckets of send_cap (vertex, parent) pairs, indexed by owner
+  unsigned int* send_count;  // world counters, 32 uints (128 bytes) apart
+  int64_t send_cap;
 };
 
 struct Tuning {

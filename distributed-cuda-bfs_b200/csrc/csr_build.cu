@@ -217,13 +217,13 @@ static int bits_for(int64_t n) {
 }
 
 Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64_t n, int64_t row_begin,
-                        int64_t row_end, bool partitioned, int dedup, cudaStream_t stream,
+                        int64_t row_end, bool partitioned, int dedup, int64_t nwords_override, cudaStream_t stream,
                         BuiltCsr* out, int64_t* launches) {
   *out = BuiltCsr();
   const int64_t nrows = row_end - row_begin;
   const int vbits = bits_for(n);
   const int rbits = bits_for(nrows > 0 ? nrows : 1);
-  const int64_t nwords = ((nrows + 31) / 32 + 3) / 4 * 4;
+  const int64_t nwords = nwords_override > 0 ? nwords_override : ((nrows + 31) / 32 + 3) / 4 * 4;
   out->nrows = nrows;
   out->nwords = nwords;
 
@@ -288,7 +288,8 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   B2_CUDA(cudaMalloc(&orig_rowptr, (size_t)(nrows + 1) * sizeof(int64_t)));
   // col is read in 16-byte vectors and 16-byte-aligned bulk copies: pad both ends
   B2_CUDA(cudaMalloc(&out->col, ((size_t)entries + 64) * sizeof(int32_t)));
-  B2_CUDA(cudaMalloc(&out->orig_deg, (size_t)(nrows > 0 ? nrows : 1) * sizeof(uint32_t)));
+  B2_CUDA(cudaMalloc(&out->orig_deg, (size_t)nwords * 32 * sizeof(uint32_t)));
+  B2_CUDA(cudaMemsetAsync(out->orig_deg, 0, (size_t)nwords * 32 * sizeof(uint32_t), stream));
   B2_CUDA(cudaMalloc(&out->visited_init, (size_t)nwords * sizeof(uint32_t)));
   B2_CUDA(cudaMalloc(&out->first_nbr, (size_t)nwords * 32 * sizeof(int32_t)));
   B2_CUDA(cudaMemsetAsync(out->col + entries, 0xff, 64 * sizeof(int32_t), stream));
@@ -318,6 +319,20 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   cudaFree(scratch);
   cudaFree(counters);
   cudaFree(bad);
+  return Status();
+}
+
+__global__ void __launch_bounds__(kBlock) row_degrees_kernel(const int64_t* __restrict__ rowptr, int64_t nrows,
+                                                             int32_t* __restrict__ deg) {
+  for (int64_t v = (int64_t)blockIdx.x * kBlock + threadIdx.x; v < nrows; v += (int64_t)gridDim.x * kBlock)
+    deg[v] = (int32_t)(rowptr[v + 1] - rowptr[v]);
+}
+
+Status row_degrees_device(const int64_t* rowptr, int64_t nrows, int32_t* deg, cudaStream_t stream) {
+  if (nrows <= 0) return Status();
+  const int64_t blocks = (nrows + kBlock - 1) / kBlock;
+  row_degrees_kernel<<<(int)(blocks < (int64_t)kSMs * 8 ? blocks : (int64_t)kSMs * 8), kBlock, 0, stream>>>(rowptr, nrows, deg);
+  B2_CUDA(cudaGetLastError());
   return Status();
 }
 

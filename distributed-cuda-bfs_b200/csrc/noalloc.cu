@@ -125,6 +125,10 @@ int b2bfs_search_noalloc(int device, int64_t n, int64_t entries, const int64_t* 
   p.g.n = n;
   p.g.nwords = ((n + 31) / 32 + 3) / 4 * 4;
   p.g.entries = entries;
+  p.g.vbase = 0;
+  p.g.part = p.g.nwords * 32;
+  p.g.rank = 0;
+  p.g.world = 1;
   p.g.rowptr = rowptr_dev;
   p.g.col = col_dev;
   p.g.visited_init = reinterpret_cast<const uint32_t*>(base + kOffInit);
@@ -139,6 +143,11 @@ int b2bfs_search_noalloc(int device, int64_t n, int64_t entries, const int64_t* 
   p.s.wideq[0] = reinterpret_cast<int2*>(base + kOffWide0);
   p.s.wideq[1] = reinterpret_cast<int2*>(base + kOffWide1);
   p.s.ctl = reinterpret_cast<Control*>(base + kOffCtl);
+  p.s.gfrontier = nullptr;
+  p.s.seen = nullptr;
+  p.s.send_buf = nullptr;
+  p.s.send_count = nullptr;
+  p.s.send_cap = 0;
   p.tn.mode = B2BFS_MODE_TOP_DOWN;
   p.tn.alpha = 14;
   p.tn.beta = 24;

@@ -111,6 +111,8 @@ int b2bfs_csr_entries(const b2bfs_t* h, int64_t* entries);
 
 /* Per-vertex degree in the reference's multigraph = its edgesSize[] (bfs.cu:868), n x int32. */
 int b2bfs_copy_degrees(b2bfs_t* h, int32_t* deg_out);
+/* Per-vertex degree in the RESIDENT CSR (after dedup), n x int32.  Multi-rank: collective. */
+int b2bfs_copy_row_degrees(b2bfs_t* h, int32_t* deg_out);
 /* Input tuples [first, first+count) back to the host (what the loader/generator produced). */
 int b2bfs_copy_edges(b2bfs_t* h, int64_t first, int64_t count, int32_t* src_out, int32_t* dst_out);
 /* Resident CSR back to the host: rowptr has n+1 int64 entries, col has csr_entries int32. */
@@ -121,8 +123,11 @@ int b2bfs_copy_csr(b2bfs_t* h, int64_t* rowptr_out, int32_t* col_out);
  * stores CSR edge indices and never copies them back, bfs.cu:147, 439).  stats nullable.
  * Replaces runCudaQueueBfs (bfs.cu:542-629; MPI: bfs_mpi.cu:549-643) with its
  * initializeCudaBfs2 (bfs.cu:402-422) and finalizeCudaBfs (bfs.cu:424-441; bfs_mpi.cu:424-448).
- * In a multi-rank job every rank calls it with the same src; rank 0's buffers receive all n entries
- * (other ranks may pass NULL). */
+ * In a multi-rank job the call is collective: every rank calls it with the same src, the per-rank
+ * slices are allgathered over NVLink and every rank that passed a buffer receives all n entries
+ * (ranks that do not want them pass NULL; parents travel unless option "gather_parent" is 0 on all
+ * ranks).  b2bfs_copy_degrees / b2bfs_copy_row_degrees are collective in the same way;
+ * b2bfs_copy_csr returns this rank's rows. */
 int b2bfs_run(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent_out, b2bfs_stats* stats);
 
 /* Same search, results left in HBM (no device->host copy). */
