@@ -146,6 +146,26 @@ class CpuReference:
         return (dr / 2) / seconds / 1e9
 
 
+def generate_edges_threaded(oracle, kind, scale, ef, seed):
+    """The host generator over disjoint tuple ranges on all cores (input synthesis, untimed)."""
+    from concurrent.futures import ThreadPoolExecutor
+    m = int(oracle.lib().oracle_gen_num_edges(kind, scale, ef))
+    n = int(oracle.lib().oracle_gen_num_vertices(kind, scale))
+    src = np.empty(m, np.int32)
+    dst = np.empty(m, np.int32)
+    threads = max(1, min(os.cpu_count() or 1, 32))
+    cuts = [m * i // threads for i in range(threads + 1)]
+
+    def work(i):
+        a, b = cuts[i], cuts[i + 1]
+        if b > a:
+            oracle.lib().oracle_generate_edges(kind, scale, ef, seed, a, b - a, src[a:b], dst[a:b])
+
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(work, range(threads)))
+    return n, src, dst
+
+
 def run_reference_arm(args):
     """--impl reference: the reference's CPU implementation of the path, host cores only."""
     import oracle
@@ -153,7 +173,7 @@ def run_reference_arm(args):
     if rank != 0:
         return
     kind = KINDS[args.kind]
-    n, src, dst = oracle.generate_edges(kind, args.scale, args.ef, args.seed)
+    n, src, dst = generate_edges_threaded(oracle, kind, args.scale, args.ef, args.seed)
     cpu = CpuReference(n, src, dst)
     nl = nonloop_degree(n, src, dst)
     giant, _ = cpu.search(int(np.argmax(nl)))  # untimed: membership of the largest component
@@ -195,12 +215,19 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the product has no CPU path (use --impl reference for the CPU baseline)")
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    if world > 1 or args.gpus > 1:
-        raise SystemExit("bench.py: multi-GPU arm not wired yet in this build")
+    rank = int(os.environ.get("RANK", "0"))
     dev = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(dev)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", dev))
+        ident = [b2.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ident, src=0)  # side channel for the library's own communicator
+        h = b2.Bfs(dev, rank=rank, world=world, nccl_id=ident[0], dedup=int(not args.no_dedup), gather_parent=0)
+    else:
+        h = b2.Bfs(dev, dedup=int(not args.no_dedup))
     kind = KINDS[args.kind]
-    h = b2.Bfs(dev, dedup=int(not args.no_dedup))
     h.set_option("mode", b2.MODE_TOP_DOWN if args.mode == "td" else b2.MODE_DIRECTION_OPT)
     h.set_option("engine", b2.ENGINE_STEPWISE if args.engine == "stepwise" else b2.ENGINE_FUSED)
     t0 = time.perf_counter()
@@ -208,41 +235,56 @@ def run_ours(args):
     torch.cuda.synchronize()
     build_s = time.perf_counter() - t0
     n, m = h.num_vertices, h.num_input_edges
-    # degree in the resident CSR: with dedup (default) self-loops are gone, so a vertex whose only
-    # tuples are self-loops is not a legal Graph500 root
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(values):
+        t = torch.tensor(values, dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.cpu().numpy()
+
+    # roots: the same on every rank (row degrees and the giant-component mask are gathered collectively)
     if args.no_dedup:
         es, ed = h.edges()
         deg = nonloop_degree(n, es, ed)
         del es, ed
     else:
-        deg = np.diff(h.csr(rowptr_only=True))
-    giant, _ = h.run(int(np.argmax(deg)))  # untimed: membership of the largest component
-    roots = pick_roots(deg, args.steps + args.warmup, args.root_seed, giant != b2.INT_MAX)
-    warm, timed = roots[:args.warmup], roots[args.warmup:args.warmup + args.steps]
+        deg = h.row_degrees()
     pinned = b2.PinnedArray(n, np.int32)
+    h.run_collective(int(np.argmax(deg)), depth_out=pinned.array)  # untimed: membership of the largest component
+    roots = pick_roots(deg, args.steps + args.warmup, args.root_seed, pinned.array != b2.INT_MAX)
+    warm, timed = roots[:args.warmup], roots[args.warmup:args.warmup + args.steps]
+    out_buf = pinned.array if rank == 0 else None
 
     for r in warm:
         h.run_device(r)
-        h.run(r, depth_out=pinned.array)
+        h.run_collective(r, depth_out=out_buf)
 
     # ---- device-resident region: value + roofline
     stats = []
     with ClockSampler(dev) as clk:
-        torch.cuda.synchronize()
+        barrier()
         w0 = time.perf_counter()
         for r in timed:
             stats.append(h.run_device(r))
-        torch.cuda.synchronize()
+        barrier()
         wall_dev = time.perf_counter() - w0
-        # ---- end-to-end region: host buffers, D2H inside the timed call
+        # ---- end-to-end region: host buffers, gather + D2H inside the timed call
         e2e = []
-        torch.cuda.synchronize()
+        barrier()
         for r in timed:
             t1 = time.perf_counter()
-            _, st = h.run(r, depth_out=pinned.array)
+            st = h.run_collective(r, depth_out=out_buf)
             e2e.append((time.perf_counter() - t1, st))
-        torch.cuda.synchronize()
-    ms = np.array([s["search_ms"] for s in stats])
+        barrier()
+    ms = max_over_ranks([s["search_ms"] for s in stats])          # device time, max over ranks per step
+    e2e_s = max_over_ranks([sec for sec, _ in e2e])
+    wall_dev = float(max_over_ranks([wall_dev])[0])
+    launches = int(max_over_ranks([float(sum(s["kernel_launches"] for s in stats))])[0])
     m_r = np.array([s["reached_entries"] / 2 for s in stats])
     teps = m_r / (ms * 1e-3) / 1e9
     value = hmean(teps)
@@ -253,30 +295,31 @@ def run_ours(args):
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             t = json.load(f)
-            if t.get("scale") == args.scale and t.get("kind") == args.kind:
+            if t.get("scale") == args.scale and t.get("kind") == args.kind and world == 1:
                 traffic = t.get("dram_bytes_per_launch")
     except Exception:
         pass
-    e2e_teps = np.array([(st["reached_entries"] / 2) / sec / 1e9 for sec, st in e2e])
-    launches = int(sum(s["kernel_launches"] for s in stats))
+    e2e_teps = m_r / e2e_s / 1e9
+    kernel = ("bfs_fused_kernel" if args.engine == "fused" else "stepwise phases") if world == 1 else \
+        "multi-rank phases (top_down_multi / bottom_up / apply_remote) + NCCL"
 
-    line = {"metric": METRIC, "value": value, "unit": "GTEPS", "n_gpus": 1, "steps": len(timed), "warmup": len(warm),
+    line = {"metric": METRIC, "value": value, "unit": "GTEPS", "n_gpus": world, "steps": len(timed), "warmup": len(warm),
             "ms_per_step": float(ms.mean()), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int32", "data": "synthetic", "config": workload_config(args, n, m),
             "gteps_min": float(teps.min()), "gteps_median": float(np.median(teps)), "gteps_max": float(teps.max()),
             "levels_mean": float(np.mean([s["levels"] for s in stats])),
             "bu_levels_mean": float(np.mean([s["bu_levels"] for s in stats])),
-            "build_s": build_s, "csr_entries": h.csr_entries, "wall_ms_per_step": 1e3 * wall_dev / len(timed),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_kind": f"of {peak_kind}", "kernel": "bfs_fused_kernel" if args.engine == "fused" else "stepwise phases",
-                         "algorithmic_bytes_per_launch": float(b_alg.mean())},
+            "build_s": build_s, "csr_entries_rank0": h.csr_entries, "wall_ms_per_step": 1e3 * wall_dev / len(timed),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s",
+                         "frac": achieved / (peak * world), "traffic": traffic, "peak_kind": f"of {peak_kind} x{world} GPUs",
+                         "kernel": kernel, "algorithmic_bytes_per_launch": float(b_alg.mean())},
             "e2e": {"value": hmean(e2e_teps), "unit": "GTEPS", "h2d_bytes_per_step": 8,
                     "d2h_bytes_per_step": int(np.mean([st["d2h_bytes"] for _, st in e2e])),
-                    "ms_per_step": 1e3 * float(np.mean([sec for sec, _ in e2e]))},
+                    "ms_per_step": 1e3 * float(e2e_s.mean())},
             "gpu_launches": launches, "clocks": clk.summary()}
 
-    # ---- CPU baseline + parity check on a bounded sample of the same roots
-    if not args.no_cpu_baseline:
+    # ---- CPU baseline + parity check on a bounded sample of the same roots (N = 1 only)
+    if not args.no_cpu_baseline and world == 1:
         src, dst = h.edges()
         cpu = CpuReference(n, src, dst)
         cteps, checked, t_start = [], 0, time.perf_counter()
@@ -295,7 +338,11 @@ def run_ours(args):
                                           f"full graph (~{args.cpu_budget:.0f} s budget); depths bit-exact vs the GPU on all {checked}"}
     pinned.free()
     h.close()
-    print(json.dumps(line), flush=True)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 def main():
@@ -304,8 +351,10 @@ def main():
     ap.add_argument("--steps", type=int, default=64)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--kind", default="rmat", choices=list(KINDS))
-    ap.add_argument("--scale", type=int, default=22)
+    ap.add_argument("--kind", default=None, choices=list(KINDS),
+                    help="default: rmat on 1 GPU (BASELINE configs[1]); kron (RMAT with scrambled labels, so a contiguous "
+                         "1-D partition is balanced) on several")
+    ap.add_argument("--scale", type=int, default=None, help="default: 22 + log2(gpus) — weak scaling, fixed tuples per GPU")
     ap.add_argument("--ef", type=int, default=16)
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--root-seed", type=int, default=2)
@@ -316,6 +365,14 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU baseline work (ours arm); 0 = default 150 s in the reference arm")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    if args.impl == "ours" and world != args.gpus and world == 1 and args.gpus > 1:
+        raise SystemExit("bench.py: --gpus N > 1 must be launched with torch.distributed.run (one process per GPU)")
+    args.gpus = world if args.impl == "ours" else args.gpus
+    if args.kind is None:
+        args.kind = "rmat" if args.gpus == 1 else "kron"
+    if args.scale is None:
+        args.scale = 22 + max(0, int(np.log2(max(args.gpus, 1))))
     if args.impl == "reference":
         if args.cpu_budget == 20.0:
             args.cpu_budget = 0

@@ -272,6 +272,13 @@ class Bfs:
                                     parent.ctypes.data if parent is not None else None, C.byref(st)))
         return (depth, parent, st.as_dict()) if parent is not None else (depth, st.as_dict())
 
+    def run_collective(self, src: int, depth_out=None):
+        """Multi-rank: every rank calls this; only ranks passing a buffer receive the n depths."""
+        st = Stats()
+        self._check(lib().b2bfs_run(self._h, int(src), depth_out.ctypes.data if depth_out is not None else None,
+                                    None, C.byref(st)))
+        return st.as_dict()
+
     def run_device(self, src: int):
         st = Stats()
         self._check(lib().b2bfs_run_device(self._h, int(src), C.byref(st)))
