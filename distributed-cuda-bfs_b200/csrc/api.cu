@@ -41,6 +41,13 @@ struct b2bfs {
   int2* send_buf = nullptr;
   unsigned int* send_count = nullptr;
   int32_t* gather_tmp = nullptr;  // world * part ints: allgather staging for depth / parent / degrees
+  // peer-memory engine: this rank's exchange region and the IPC mappings of the peers' regions
+  int multi_engine = 0;            // 0: peer memory (falls back to 1 when IPC is unavailable), 1: NCCL per level
+  bool p2p_ready = false;
+  unsigned char* xregion = nullptr;
+  unsigned char* xpeer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  int grid_multi = 0;
+  unsigned long long search_seq = 0;
 };
 
 static thread_local std::string g_create_error;
@@ -74,6 +81,19 @@ static void free_search_state(b2bfs* h) {
 }
 
 static void free_multi_state(b2bfs* h) {
+  if (h->xregion) {
+    // collective: unmap the peers' regions, make sure every rank has done so, then free our own
+    for (int r = 0; r < h->world; ++r)
+      if (r != h->rank && h->xpeer[r]) cudaIpcCloseMemHandle(h->xpeer[r]);
+    if (h->mc.comm && h->mc.stats_send) {
+      h->mc.nccl->AllReduce(h->mc.stats_send, h->mc.stats_all, 1, ncclUint64, ncclSum, h->mc.comm, h->stream);
+      cudaStreamSynchronize(h->stream);
+    }
+    cudaFree(h->xregion);
+    h->xregion = nullptr;
+    for (int r = 0; r < 8; ++r) h->xpeer[r] = nullptr;
+    h->p2p_ready = false;
+  }
   cudaFree(h->gfrontier);
   cudaFree(h->seen);
   cudaFree(h->send_buf);
@@ -159,6 +179,38 @@ static int finish_load(b2bfs* h) {
     API_CUDA(h, cudaStreamSynchronize(h->stream));
     h->mc.entries_global = (int64_t)h->mc.stats_host[0];
     h->mc.n_global = h->n;
+    // peer-memory engine: one exchange region per rank, mapped into every peer with CUDA IPC
+    // (the handles travel through the NCCL communicator, so no extra side channel is needed)
+    unsigned long long ok = 1;
+    cudaIpcMemHandle_t handles[8];
+    const size_t xbytes = xchg_region_bytes(h->world, h->part);
+    if (cudaMalloc(&h->xregion, xbytes) != cudaSuccess || cudaMemsetAsync(h->xregion, 0, xbytes, h->stream) != cudaSuccess ||
+        cudaIpcGetMemHandle(&handles[h->rank], h->xregion) != cudaSuccess) {
+      ok = 0;
+      cudaGetLastError();
+      memset(&handles[h->rank], 0, sizeof(cudaIpcMemHandle_t));
+    }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    unsigned char* hbuf = reinterpret_cast<unsigned char*>(h->gather_tmp);
+    API_CUDA(h, cudaMemcpyAsync(hbuf + 64 * h->rank, &handles[h->rank], 64, cudaMemcpyHostToDevice, h->stream));
+    API_NCCL(h, h->mc.nccl->AllGather(hbuf + 64 * h->rank, hbuf, 64, ncclUint8, h->mc.comm, h->stream));
+    API_CUDA(h, cudaMemcpyAsync(handles, hbuf, 64 * (size_t)k, cudaMemcpyDeviceToHost, h->stream));
+    API_CUDA(h, cudaStreamSynchronize(h->stream));
+    for (int r = 0; r < h->world && ok; ++r) {
+      if (r == h->rank) { h->xpeer[r] = h->xregion; continue; }
+      void* ptr = nullptr;
+      if (cudaIpcOpenMemHandle(&ptr, handles[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+        ok = 0;
+        cudaGetLastError();
+      }
+      h->xpeer[r] = static_cast<unsigned char*>(ptr);
+    }
+    // every rank must agree on the engine
+    API_CUDA(h, cudaMemcpyAsync(h->mc.stats_send, &ok, sizeof(ok), cudaMemcpyHostToDevice, h->stream));
+    API_NCCL(h, h->mc.nccl->AllReduce(h->mc.stats_send, h->mc.stats_all, 1, ncclUint64, ncclMin, h->mc.comm, h->stream));
+    API_CUDA(h, cudaMemcpyAsync(h->mc.stats_host, h->mc.stats_all, sizeof(ok), cudaMemcpyDeviceToHost, h->stream));
+    API_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->p2p_ready = h->mc.stats_host[0] == 1 && h->xregion != nullptr;
   }
   API_CUDA(h, cudaStreamSynchronize(h->stream));
   h->has_graph = true;
@@ -197,6 +249,10 @@ static BfsParams make_params(const b2bfs* h) {
   p.s.send_buf = h->send_buf;
   p.s.send_count = h->send_count;
   p.s.send_cap = h->part;
+  const bool p2p = multi && h->p2p_ready && h->multi_engine == 0;
+  for (int r = 0; r < 8; ++r) p.s.xbase[r] = p2p ? h->xpeer[r] : nullptr;
+  p.g.n_global = h->n;
+  p.g.entries_global = multi ? (unsigned long long)h->mc.entries_global : (unsigned long long)h->csr.entries;
   p.tn.mode = h->mode;
   p.tn.alpha = h->alpha;
   p.tn.beta = h->beta;
@@ -270,6 +326,12 @@ int b2bfs_create_rank(b2bfs_t** out, int device, int rank, int world, const void
     *out = nullptr;
     return fail(nullptr, B2BFS_ERR_COMM, msg);
   }
+  Status gs = multi_grid_size(device, &h->grid_multi);
+  if (!gs.ok()) {
+    b2bfs_destroy(h);
+    *out = nullptr;
+    return fail(nullptr, gs);
+  }
   cudaError_t e = cudaMalloc(&h->mc.stats_send, 16 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaMalloc(&h->mc.stats_all, (size_t)world * 16 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaMallocHost(&h->mc.stats_host, (size_t)world * 16 * sizeof(unsigned long long));
@@ -291,6 +353,7 @@ int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
   else if (k == "mode" && (value == B2BFS_MODE_DIRECTION_OPT || value == B2BFS_MODE_TOP_DOWN)) h->mode = (int)value;
   else if (k == "engine" && (value == B2BFS_ENGINE_FUSED || value == B2BFS_ENGINE_STEPWISE)) h->engine = (int)value;
   else if (k == "gather_parent" && (value == 0 || value == 1)) h->gather_parent = (int)value;
+  else if (k == "multi_engine" && (value == 0 || value == 1)) h->multi_engine = (int)value;
   else if (k == "alpha" && value >= 1 && value <= (1 << 20)) h->alpha = (int)value;
   else if (k == "beta" && value >= 1 && value <= (1 << 20)) h->beta = (int)value;
   else return fail(h, B2BFS_ERR_ARG, "unknown option or value out of range: " + k);
@@ -308,6 +371,7 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   else if (k == "beta") *value = h->beta;
   else if (k == "grid") *value = h->grid;
   else if (k == "gather_parent") *value = h->gather_parent;
+  else if (k == "multi_engine") *value = (h->world > 1 && h->p2p_ready && h->multi_engine == 0) ? 0 : 1;
   else if (k == "rank") *value = h->rank;
   else if (k == "world") *value = h->world;
   else if (k == "local_rows") *value = h->nloc;
@@ -468,7 +532,9 @@ static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent
   int64_t launches = 0;
   MultiResult mr;
   API_CUDA(h, cudaEventRecord(h->ev0, h->stream));
-  Status s = multi ? run_multi(p, h->mc, src, h->grid, h->stream, &mr)
+  const bool p2p = multi && p.s.xbase[0] != nullptr;
+  Status s = p2p ? run_fused_multi(p, src, (++h->search_seq) << 32, h->grid_multi, h->stream, &mr.launches)
+           : multi ? run_multi(p, h->mc, src, h->grid, h->stream, &mr)
            : (h->engine == B2BFS_ENGINE_FUSED) ? run_fused(p, src, h->grid, h->stream, &launches)
                                                : run_stepwise(p, src, h->grid, h->stream, h->pinned_ctl, &launches);
   if (!s.ok()) return fail(h, s);
@@ -509,9 +575,11 @@ static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent
     float ms = 0.f;
     API_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
     const Control* c = h->pinned_ctl;
-    stats->levels = multi ? mr.levels : c->result.levels;
-    stats->td_levels = multi ? mr.td_levels : c->result.td_levels;
-    stats->bu_levels = multi ? mr.bu_levels : c->result.bu_levels;
+    if (p2p && c->error) return fail(h, B2BFS_ERR_COMM, "a cross-GPU wait timed out inside the search kernel (peer rank missing?)");
+    const bool host_loop = multi && !p2p;
+    stats->levels = host_loop ? mr.levels : c->result.levels;
+    stats->td_levels = host_loop ? mr.td_levels : c->result.td_levels;
+    stats->bu_levels = host_loop ? mr.bu_levels : c->result.bu_levels;
     stats->reserved0 = 0;
     stats->reached_vertices = (int64_t)c->reached_vertices;
     stats->reached_entries = (int64_t)c->reached_entries;

@@ -239,7 +239,13 @@ __device__ __forceinline__ void remote_flush(const BfsParams& p, RemoteStage& rs
       const int leader = __ffs(m) - 1;
       if ((int)lane == leader) base = atomicAdd(&p.s.send_count[d * 32], (unsigned)__popc(m));
       base = __shfl_sync(0xffffffffu, base, leader);
-      if (owner == d) p.s.send_buf[(int64_t)d * p.s.send_cap + base + __popc(m & ((1u << lane) - 1u))] = e;
+      if (owner == d) {
+        const int64_t pos = base + __popc(m & ((1u << lane) - 1u));
+        if (p.s.xbase[0])  // straight into rank d's inbox bucket for this rank, over NVLink
+          reinterpret_cast<int2*>(p.s.xbase[d] + xchg_off_inbox(p.g.world, p.g.part))[(int64_t)p.g.rank * p.s.send_cap + pos] = e;
+        else
+          p.s.send_buf[(int64_t)d * p.s.send_cap + pos] = e;
+      }
     }
   }
   __syncwarp();
@@ -573,10 +579,11 @@ __device__ __forceinline__ void bu_tier2(const BfsParams& p, int level, const ui
   __syncwarp();
 }
 
-__device__ __forceinline__ void phase_bottom_up(const BfsParams& p, const LoopState& st, WarpStage* stage) {
+__device__ __forceinline__ void phase_bottom_up(const BfsParams& p, const LoopState& st, WarpStage* stage,
+                                                const uint32_t* frontier_override = nullptr) {
   const int level = st.level;
   // multi-rank: probe the allgathered frontier of all ranks (global ids), write this rank's slice
-  const uint32_t* fr = p.s.gfrontier ? p.s.gfrontier : p.s.bitmap[st.fb];
+  const uint32_t* fr = frontier_override ? frontier_override : p.s.gfrontier ? p.s.gfrontier : p.s.bitmap[st.fb];
   uint32_t* nx = p.s.bitmap[st.fb ^ 1];
   LevelSlot* ns = &p.s.ctl->slot[(level + 1) & 3];
   const unsigned lane = lane_id();
@@ -912,6 +919,174 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
 }
 
 // ---------------------------------------------------------------------------------------------
+// peer-memory engine: the whole MULTI-RANK search in one persistent cooperative kernel per GPU.
+// Each rank's kernel writes what its peers need straight into their memory over NVLink (CUDA IPC
+// mappings of one exchange region per rank) — frontier-bitmap slices after a bottom-up level,
+// (vertex, parent) pairs during a top-down level — and the per-level collective shrinks to a record
+// exchange: every rank stores a 128-byte record (queue tails, degree sum, per-peer pair counts) into
+// every peer's record table, the last word being the epoch number, and waits until the records of
+// all peers for this epoch have landed in its own table.  Records carry the counters, so every rank
+// takes the same decisions from the same numbers without a host in the loop.
+// Requires one rank per physical GPU (the kernels of different ranks wait for one another).
+// Replaces the per-level MPI_Sendrecv + MPI_Allreduce round trips of bfs_mpi.cu:612-621.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__device__ __forceinline__ volatile unsigned long long* xrecord(const BfsParams& p, int on_rank, unsigned long long epoch,
+                                                                int from_rank) {
+  return reinterpret_cast<volatile unsigned long long*>(p.s.xbase[on_rank] + xchg_off_records(p.g.world, p.g.part)) +
+         ((epoch & 3) * 8 + from_rank) * 16;
+}
+
+// All ranks call this the same number of times.  On return sums[0..4] = totals over ranks of
+// (narrow tail, wide tail, degree sum, bottom-up finds, source degree) of `slot`, mine[0..1] = this
+// rank's own tails and incoming[s] = pairs rank s staged for this rank.
+__device__ __forceinline__ void cross_exchange(const BfsParams& p, cg::grid_group& grid, unsigned long long epoch, int slot,
+                                               unsigned long long* sums, unsigned int* incoming, int* failed) {
+  __shared__ unsigned long long rec_s[8][16];
+  const int k = p.g.world, me = p.g.rank;
+  grid.sync();  // everything this GPU wrote for its peers during the phase has been issued
+  if (blockIdx.x == 0 && (int)threadIdx.x < k) {
+    const int d = threadIdx.x;
+    const LevelSlot* s = &p.s.ctl->slot[slot & 3];
+    volatile unsigned long long* dst = xrecord(p, d, epoch, me);
+    __threadfence_system();
+    dst[0] = ld_volatile(&s->q_count);
+    dst[1] = ld_volatile(&s->wide_count);
+    dst[2] = ld_volatile(&s->edges);
+    dst[3] = ld_volatile(&s->bu_count);
+    dst[4] = (unsigned long long)p.s.ctl->src_degree;
+    for (int j = 0; j < 8; ++j) dst[8 + j] = j < k ? ld_volatile(&p.s.send_count[j * 32]) : 0u;
+    __threadfence_system();
+    dst[15] = epoch;  // arrival flag, after the payload
+    volatile unsigned long long* src = xrecord(p, me, epoch, d);
+    const unsigned long long t0 = global_ns();
+    while (src[15] != epoch) {
+      if (global_ns() - t0 > 4000000000ull) {  // 4 s: a peer died or never launched
+        p.s.ctl->error = 1;
+        break;
+      }
+    }
+    __threadfence_system();
+  }
+  grid.sync();  // the records of every rank are in this GPU's memory
+  if ((int)threadIdx.x < k * 16) rec_s[threadIdx.x >> 4][threadIdx.x & 15] = xrecord(p, me, epoch, threadIdx.x >> 4)[threadIdx.x & 15];
+  __syncthreads();
+  for (int i = 0; i < 5; ++i) sums[i] = 0;
+  for (int r = 0; r < k; ++r) {
+    for (int i = 0; i < 5; ++i) sums[i] += rec_s[r][i];
+    incoming[r] = (unsigned int)rec_s[r][8 + me];
+  }
+  sums[5] = rec_s[me][0];
+  sums[6] = rec_s[me][1];
+  *failed = *reinterpret_cast<volatile int*>(&p.s.ctl->error);
+  __syncthreads();
+}
+
+// copy this rank's next-frontier slice (bitmap[0]) into buffer `which` of every rank's frontier bitmap
+__device__ __forceinline__ void push_frontier_slice(const BfsParams& p, int which) {
+  const int64_t words4 = p.g.part / 128;  // uint4 groups in a slice
+  const uint4* mine = reinterpret_cast<const uint4*>(p.s.bitmap[0]);
+  const int64_t tid = (int64_t)blockIdx.x * kBlock + threadIdx.x, nthreads = (int64_t)gridDim.x * kBlock;
+  const size_t off = (size_t)which * xchg_frontier_bytes(p.g.world, p.g.part) + (size_t)p.g.rank * (size_t)p.g.part / 8;
+  for (int64_t i = tid; i < words4 * p.g.world; i += nthreads) {
+    const int d = (int)(i / words4);
+    const int64_t j = i - (int64_t)d * words4;
+    reinterpret_cast<uint4*>(p.s.xbase[d] + off)[j] = mine[j];
+  }
+}
+
+__global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_kernel(BfsParams p, int64_t src,
+                                                                                      unsigned long long epoch) {
+  __shared__ WarpStage stage[kWarpsPerBlock];
+  __shared__ RemoteStage rstage[kWarpsPerBlock];
+  cg::grid_group grid = cg::this_grid();
+  const int k = p.g.world, me = p.g.rank;
+  const int64_t src_local = (src / p.g.part == me) ? src - p.g.vbase : -1;
+  {  // reset: local state as on one GPU, plus the replicated `seen` filter
+    uint4* s4 = reinterpret_cast<uint4*>(p.s.seen);
+    const int64_t n4 = (int64_t)k * p.g.part / 128;
+    for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n4; i += (int64_t)gridDim.x * kBlock)
+      s4[i] = make_uint4(0, 0, 0, 0);
+    if (blockIdx.x == 0 && threadIdx.x < 8) p.s.send_count[threadIdx.x * 32] = 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) p.s.ctl->error = 0;
+  }
+  phase_init(p, src_local);
+  unsigned long long sums[7];
+  unsigned int incoming[8];
+  int failed = 0;
+  cross_exchange(p, grid, ++epoch, 0, sums, incoming, &failed);
+
+  LoopState st;
+  st.level = 0; st.mode = 0; st.fb = 1; st.done = failed;  // fb = 1: bottom-up writes bitmap[0], this rank's slice
+  st.cur_q = (unsigned)sums[5];
+  st.cur_wide = (unsigned)sums[6];
+  st.prev_nf = 1;
+  st.unexplored = p.g.entries_global - sums[4];
+  st.td_levels = st.bu_levels = 0;
+  int gcur = 0;  // frontier bitmap buffer bottom-up reads
+
+  while (!st.done) {
+    unsigned long long nf = 0, mf = 0;
+    if (st.mode == 0) {
+      phase_top_down<true>(p, st, stage, blockIdx.x, gridDim.x, rstage);
+      cross_exchange(p, grid, ++epoch, st.level + 1, sums, incoming, &failed);  // pair counts
+      const int2* inbox = reinterpret_cast<const int2*>(p.s.xbase[me] + xchg_off_inbox(k, p.g.part));
+      for (int s = 0; s < k; ++s)
+        if (s != me && incoming[s]) phase_apply_remote(p, st, stage, inbox + (int64_t)s * p.s.send_cap, incoming[s]);
+      if (blockIdx.x == 0 && threadIdx.x < 8) p.s.send_count[threadIdx.x * 32] = 0;  // all counts were read above
+      cross_exchange(p, grid, ++epoch, st.level + 1, sums, incoming, &failed);  // tails after the arrivals
+      nf = sums[0] + sums[1];
+      mf = sums[2];
+      st.cur_q = (unsigned)sums[5];
+      st.cur_wide = (unsigned)sums[6];
+      st.td_levels++;
+    } else {
+      phase_bottom_up(p, st, stage,
+                      reinterpret_cast<const uint32_t*>(p.s.xbase[me] + (size_t)gcur * xchg_frontier_bytes(k, p.g.part)));
+      grid.sync();  // the slice is complete (late finds are OR-ed in by any CTA)
+      push_frontier_slice(p, gcur ^ 1);
+      cross_exchange(p, grid, ++epoch, st.level + 1, sums, incoming, &failed);
+      gcur ^= 1;
+      nf = sums[3];
+      st.bu_levels++;
+    }
+    st.unexplored = mf > st.unexplored ? 0ull : st.unexplored - mf;
+    st.level++;
+    if (nf == 0 || failed) {
+      st.done = 1;
+    } else if (st.mode == 0) {
+      if (p.tn.mode == B2BFS_MODE_DIRECTION_OPT && mf > st.unexplored / (unsigned)p.tn.alpha && nf >= st.prev_nf) {
+        st.mode = 1;
+        phase_queue_to_bitmap(p, st);  // own new frontier -> bitmap[0] (all-zero while top-down runs)
+        grid.sync();
+        push_frontier_slice(p, gcur ^ 1);
+        cross_exchange(p, grid, ++epoch, st.level, sums, incoming, &failed);
+        gcur ^= 1;
+        if (failed) st.done = 1;
+      }
+    } else if (nf < (unsigned long long)p.g.n_global / (unsigned)p.tn.beta && nf < st.prev_nf) {
+      st.mode = 0;
+      phase_bitmap_to_queue(p, st, stage);
+      grid.sync();
+      const LevelSlot* cs = &p.s.ctl->slot[st.level & 3];
+      st.cur_q = ld_volatile(&cs->q_count);
+      st.cur_wide = ld_volatile(&cs->wide_count);
+    }
+    st.prev_nf = nf;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    p.s.ctl->result.levels = st.level;
+    p.s.ctl->result.td_levels = st.td_levels;
+    p.s.ctl->result.bu_levels = st.bu_levels;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // after the search (outside the timed window): V_r and D_r for the metric
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock) reach_stats_kernel(int64_t n, const int32_t* __restrict__ depth,
@@ -942,6 +1117,26 @@ Status run_fused(const BfsParams& p, int64_t src, int grid, cudaStream_t stream,
   void* args[] = {&pp, &s};
   B2_CUDA(cudaLaunchCooperativeKernel((const void*)bfs_fused_kernel, dim3(grid), dim3(kBlock), args, 0, stream));
   if (launches) *launches += 1;
+  return Status();
+}
+
+Status run_fused_multi(const BfsParams& p, int64_t src, unsigned long long epoch_base, int grid, cudaStream_t stream,
+                       int64_t* launches) {
+  BfsParams pp = p;
+  int64_t s = src;
+  unsigned long long e = epoch_base;
+  void* args[] = {&pp, &s, &e};
+  B2_CUDA(cudaLaunchCooperativeKernel((const void*)bfs_fused_multi_kernel, dim3(grid), dim3(kBlock), args, 0, stream));
+  if (launches) *launches += 1;
+  return Status();
+}
+
+Status multi_grid_size(int device, int* grid_out) {
+  int per_sm = 0, sms = 0;
+  B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bfs_fused_multi_kernel, kBlock, 0));
+  B2_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+  if (per_sm < 1) return make_error(B2BFS_ERR_CUDA, "bfs_fused_multi_kernel does not fit on an SM");
+  *grid_out = per_sm * sms;
   return Status();
 }
 

@@ -59,6 +59,8 @@ struct GraphView {
   int64_t vbase;             // global id of local row 0 (0 on a single GPU); col[] holds GLOBAL ids
   int64_t part;              // rows per rank of the 1-D partition (multiple of 128); owner(v) = v / part
   int rank, world;
+  int64_t n_global;          // all vertices
+  unsigned long long entries_global;  // resident entries over all ranks
   const int64_t* rowptr;     // n+1 offsets into col
   const int32_t* col;        // neighbour ids, sorted ascending inside a row
   const uint32_t* visited_init;  // bit set = never scan this vertex bottom-up (degree 0, or id >= n)
@@ -106,6 +108,7 @@ struct Control {
   alignas(128) unsigned long long group_barrier;         // monotonic arrival counter of the small-frontier group
   alignas(128) LoopState resume_state;                   // what the group decided, for the CTAs that waited
   int resume_conversion;
+  int error;                                             // peer-memory engine: a cross-GPU wait timed out
   unsigned int group_exit_seq;                           // bumped when the group leaves its level loop
   int trace_len;                                         // fused engine: per-phase timestamps of CTA 0
   TraceRec trace[kTraceCap];
@@ -125,7 +128,22 @@ struct SearchView {
   int2* send_buf;            // world buckets of send_cap (vertex, parent) pairs, indexed by owner
   unsigned int* send_count;  // world counters, 32 uints (128 bytes) apart
   int64_t send_cap;
+  // peer-memory engine: base of every rank's exchange region (own one included), mapped with CUDA
+  // IPC; all nullptr when exchanges go through NCCL.  Layout of a region (same on every rank):
+  //   [2][world * part/8 B]  frontier bitmaps, ping-pong
+  //   [world][part] int2     inbox: bucket s holds the (vertex, parent) pairs rank s found for me
+  //   [4][8][16] u64         per-exchange records of every rank, word 15 = epoch (the arrival flag)
+  unsigned char* xbase[8];
 };
+
+__host__ __device__ inline size_t xchg_frontier_bytes(int world, int64_t part) { return (size_t)world * (size_t)part / 8; }
+__host__ __device__ inline size_t xchg_off_inbox(int world, int64_t part) { return 2 * xchg_frontier_bytes(world, part); }
+__host__ __device__ inline size_t xchg_off_records(int world, int64_t part) {
+  return xchg_off_inbox(world, part) + (size_t)world * (size_t)part * sizeof(int2);
+}
+__host__ __device__ inline size_t xchg_region_bytes(int world, int64_t part) {
+  return xchg_off_records(world, part) + 4 * 8 * 16 * sizeof(unsigned long long);
+}
 
 struct Tuning {
   int mode;                  // B2BFS_MODE_*

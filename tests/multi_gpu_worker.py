@@ -36,8 +36,9 @@ def main():
         nonlocal checked
         for root in roots:
             want = oracle.bfs_serial(g, int(root))
-            for mode in (b2.MODE_DIRECTION_OPT, b2.MODE_TOP_DOWN):
+            for mode, engine in ((b2.MODE_DIRECTION_OPT, 0), (b2.MODE_TOP_DOWN, 0), (b2.MODE_DIRECTION_OPT, 1), (b2.MODE_TOP_DOWN, 1)):
                 h.set_option("mode", mode)
+                h.set_option("multi_engine", engine)  # 0: peer-memory fused kernel, 1: NCCL per level
                 depth, parent, st = h.run(int(root), want_parent=True)
                 bad = oracle.check_output(depth, want)
                 assert bad == -1, f"rank {rank} root {root} mode {mode}: vertex {bad} got {depth[bad]} want {want[bad]}"
@@ -47,6 +48,7 @@ def main():
                 assert st["levels"] == int(want[want != oracle.INT_MAX].max()) + 1
                 checked += 1
         h.set_option("mode", b2.MODE_DIRECTION_OPT)
+        h.set_option("multi_engine", 0)
 
     # synthetic graphs, generated on every rank, each keeping its own rows
     for kind, scale, ef, seed in ((1, 16, 16, 1), (0, 14, 16, 3), (2, 12, 0, 0), (1, 9, 4, 5)):
@@ -69,10 +71,11 @@ def main():
             depth, _ = h.run(s["root"])
             assert oracle.check_output(depth, np.array(s["depth"], np.int32)) == -1, (name, s["root"])
             checked += 1
+    peer = h.get_option("multi_engine") == 0
     h.close()
     dist.barrier()
     if rank == 0:
-        print(f"MULTI_GPU_OK world={world} searches_checked={checked}")
+        print(f"MULTI_GPU_OK world={world} searches_checked={checked} peer_memory_engine={'yes' if peer else 'no (NCCL fallback)'}")
     dist.destroy_process_group()
 
 
