@@ -23,7 +23,7 @@ struct b2bfs {
   std::string err;
   // options
   int dedup = 1, mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED;
-  int alpha = 14, beta = 24, keep_edges = 1, gather_parent = 1;
+  int alpha = 14, beta = 24, keep_edges = 1, gather_parent = 1, hub_first = 1;
   // graph
   bool has_graph = false;
   int64_t n = 0, m = 0;
@@ -139,7 +139,7 @@ static int finish_load(b2bfs* h) {
     h->nloc = h->n;
   }
   Status s = build_csr_device(h->d_src, h->d_dst, h->m, h->n, h->vbase, h->vbase + h->nloc, multi, h->dedup,
-                              multi ? h->part / 32 : 0, h->stream, &h->csr, &h->build_launches);
+                              h->hub_first, multi ? h->part / 32 : 0, h->stream, &h->csr, &h->build_launches);
   if (!s.ok()) {
     free_graph(h);
     return fail(h, s);
@@ -346,10 +346,11 @@ int b2bfs_create_rank(b2bfs_t** out, int device, int rank, int world, const void
 int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
   if (!h || !key) return fail(h, B2BFS_ERR_ARG, "b2bfs_set_option: null argument");
   const std::string k(key);
-  const bool graph_time = (k == "dedup" || k == "keep_edges");
+  const bool graph_time = (k == "dedup" || k == "keep_edges" || k == "hub_first");
   if (graph_time && h->has_graph) return fail(h, B2BFS_ERR_STATE, "option '" + k + "' must be set before loading a graph");
   if (k == "dedup" && (value == 0 || value == 1)) h->dedup = (int)value;
   else if (k == "keep_edges" && (value == 0 || value == 1)) h->keep_edges = (int)value;
+  else if (k == "hub_first" && (value == 0 || value == 1)) h->hub_first = (int)value;
   else if (k == "mode" && (value == B2BFS_MODE_DIRECTION_OPT || value == B2BFS_MODE_TOP_DOWN)) h->mode = (int)value;
   else if (k == "engine" && (value == B2BFS_ENGINE_FUSED || value == B2BFS_ENGINE_STEPWISE)) h->engine = (int)value;
   else if (k == "gather_parent" && (value == 0 || value == 1)) h->gather_parent = (int)value;
@@ -365,6 +366,7 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   const std::string k(key);
   if (k == "dedup") *value = h->dedup;
   else if (k == "keep_edges") *value = h->keep_edges;
+  else if (k == "hub_first") *value = h->hub_first;
   else if (k == "mode") *value = h->mode;
   else if (k == "engine") *value = h->engine;
   else if (k == "alpha") *value = h->alpha;

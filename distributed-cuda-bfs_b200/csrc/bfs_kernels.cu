@@ -1019,7 +1019,10 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
   unsigned long long sums[7];
   unsigned int incoming[8];
   int failed = 0;
+  int ntrace = 0;
+  trace_mark(p.s.ctl, ntrace, 0, -1);
   cross_exchange(p, grid, ++epoch, 0, sums, incoming, &failed);
+  trace_mark(p.s.ctl, ntrace, 0, 0);
 
   LoopState st;
   st.level = 0; st.mode = 0; st.fb = 1; st.done = failed;  // fb = 1: bottom-up writes bitmap[0], this rank's slice
@@ -1034,12 +1037,15 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
     unsigned long long nf = 0, mf = 0;
     if (st.mode == 0) {
       phase_top_down<true>(p, st, stage, blockIdx.x, gridDim.x, rstage);
+      trace_mark(p.s.ctl, ntrace, st.level, 6);
       cross_exchange(p, grid, ++epoch, st.level + 1, sums, incoming, &failed);  // pair counts
+      trace_mark(p.s.ctl, ntrace, st.level, 7);
       const int2* inbox = reinterpret_cast<const int2*>(p.s.xbase[me] + xchg_off_inbox(k, p.g.part));
       for (int s = 0; s < k; ++s)
         if (s != me && incoming[s]) phase_apply_remote(p, st, stage, inbox + (int64_t)s * p.s.send_cap, incoming[s]);
       if (blockIdx.x == 0 && threadIdx.x < 8) p.s.send_count[threadIdx.x * 32] = 0;  // all counts were read above
       cross_exchange(p, grid, ++epoch, st.level + 1, sums, incoming, &failed);  // tails after the arrivals
+      trace_mark(p.s.ctl, ntrace, st.level, 8);
       nf = sums[0] + sums[1];
       mf = sums[2];
       st.cur_q = (unsigned)sums[5];
@@ -1049,8 +1055,10 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
       phase_bottom_up(p, st, stage,
                       reinterpret_cast<const uint32_t*>(p.s.xbase[me] + (size_t)gcur * xchg_frontier_bytes(k, p.g.part)));
       grid.sync();  // the slice is complete (late finds are OR-ed in by any CTA)
+      trace_mark(p.s.ctl, ntrace, st.level, 9);
       push_frontier_slice(p, gcur ^ 1);
       cross_exchange(p, grid, ++epoch, st.level + 1, sums, incoming, &failed);
+      trace_mark(p.s.ctl, ntrace, st.level, 10);
       gcur ^= 1;
       nf = sums[3];
       st.bu_levels++;
@@ -1066,6 +1074,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
         grid.sync();
         push_frontier_slice(p, gcur ^ 1);
         cross_exchange(p, grid, ++epoch, st.level, sums, incoming, &failed);
+        trace_mark(p.s.ctl, ntrace, st.level, 3);
         gcur ^= 1;
         if (failed) st.done = 1;
       }
@@ -1073,6 +1082,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
       st.mode = 0;
       phase_bitmap_to_queue(p, st, stage);
       grid.sync();
+      trace_mark(p.s.ctl, ntrace, st.level, 4);
       const LevelSlot* cs = &p.s.ctl->slot[st.level & 3];
       st.cur_q = ld_volatile(&cs->q_count);
       st.cur_wide = ld_volatile(&cs->wide_count);

@@ -12,7 +12,8 @@ struct BuiltCsr {
   int64_t wide_items = 0;    // sum over rows with degree >= kNarrow of ceil(degree / kChunk)
   int64_t max_degree = 0;
   int64_t* rowptr = nullptr;        // nrows + 1
-  int32_t* col = nullptr;           // entries (+64 padding ints)
+  int32_t* col = nullptr;           // entries (+64 padding ints); inside a row: hubs first (descending
+                                    // floor(log2 degree)), then ascending id
   uint32_t* orig_deg = nullptr;     // nrows: the reference's edgesSize[]
   uint32_t* visited_init = nullptr; // nwords
   int32_t* first_nbr = nullptr;     // nwords * 32
@@ -22,7 +23,8 @@ Status generate_edges_device(int kind, int scale, int ef, uint64_t seed, int64_t
                              int32_t* dst, cudaStream_t stream);
 
 Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64_t n, int64_t row_begin,
-                        int64_t row_end, bool partitioned, int dedup, int64_t nwords_override, cudaStream_t stream,
+                        int64_t row_end, bool partitioned, int dedup, int hub_first, int64_t nwords_override,
+                        cudaStream_t stream,
                         BuiltCsr* out, int64_t* launches);
 
 Status row_degrees_device(const int64_t* rowptr, int64_t nrows, int32_t* deg, cudaStream_t stream);

@@ -3,7 +3,7 @@
 // Stands in for the reference's host-side loader tail and flatten loop (bfs.cu:851-875: push v onto
 // u's list and u onto v's, then concatenate rows) and for the H2D half of initCuda2
 // (bfs.cu:333-351).  Instead of n heap vectors on one host core, the 2m directed entries become
-// 64-bit keys (row << vbits | neighbour), are radix-sorted (radix_sort.cu), optionally de-duplicated
+// 64-bit keys (row | degree class of the neighbour | neighbour), are radix-sorted (radix_sort.cu), optionally de-duplicated
 // (duplicates and self-loops never change a BFS depth), and compacted into col[] while the same pass
 // derives rowptr[] from the row boundaries of the sorted keys — no per-vertex atomics.
 //
@@ -47,7 +47,8 @@ Status generate_edges_device(int kind, int scale, int ef, uint64_t seed, int64_t
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock) expand_edges_kernel(const int32_t* __restrict__ src,
                                                               const int32_t* __restrict__ dst, int64_t m, int64_t n,
-                                                              int vbits, int64_t row_begin, int64_t row_end,
+                                                              int vbits, int rshift, const uint32_t* __restrict__ degc,
+                                                              int64_t row_begin, int64_t row_end,
                                                               uint64_t* __restrict__ keys,
                                                               unsigned long long* cursor, int* bad_flag) {
   const int lane = threadIdx.x & 31;
@@ -62,10 +63,16 @@ __global__ void __launch_bounds__(kBlock) expand_edges_kernel(const int32_t* __r
       v = dst[i];
       if (u < 0 || v < 0 || u >= n || v >= n) { *bad_flag = 1; ok = false; }
     }
+    // hub-first rows: neighbours sort by descending floor(log2(degree)) before ascending id
+    uint64_t cu = 0, cv = 0;
+    if (ok && degc) {
+      cu = (uint64_t)(15 - min(15, 31 - __clz((int)max(degc[u], 1u)))) << vbits;
+      cv = (uint64_t)(15 - min(15, 31 - __clz((int)max(degc[v], 1u)))) << vbits;
+    }
     if (cursor == nullptr) {
       if (ok) {
-        keys[2 * i] = ((uint64_t)u << vbits) | (uint64_t)v;
-        keys[2 * i + 1] = ((uint64_t)v << vbits) | (uint64_t)u;
+        keys[2 * i] = ((uint64_t)u << rshift) | cv | (uint64_t)v;
+        keys[2 * i + 1] = ((uint64_t)v << rshift) | cu | (uint64_t)u;
       }
     } else {
       const bool a = ok && u >= row_begin && u < row_end;
@@ -76,8 +83,21 @@ __global__ void __launch_bounds__(kBlock) expand_edges_kernel(const int32_t* __r
       if (lane == 0 && na + nb) base = atomicAdd(cursor, (unsigned long long)(na + nb));
       base = __shfl_sync(0xffffffffu, base, 0);
       const unsigned lt = (1u << lane) - 1u;
-      if (a) keys[base + __popc(ma & lt)] = ((uint64_t)(u - row_begin) << vbits) | (uint64_t)v;
-      if (b) keys[base + na + __popc(mb & lt)] = ((uint64_t)(v - row_begin) << vbits) | (uint64_t)u;
+      if (a) keys[base + __popc(ma & lt)] = ((uint64_t)(u - row_begin) << rshift) | cv | (uint64_t)v;
+      if (b) keys[base + na + __popc(mb & lt)] = ((uint64_t)(v - row_begin) << rshift) | cu | (uint64_t)u;
+    }
+  }
+}
+
+// multigraph degree of every vertex straight from the tuples (only its log2 class is used)
+__global__ void __launch_bounds__(kBlock) degree_count_kernel(const int32_t* __restrict__ src,
+                                                              const int32_t* __restrict__ dst, int64_t m, int64_t n,
+                                                              uint32_t* __restrict__ degc) {
+  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < m; i += (int64_t)gridDim.x * kBlock) {
+    const int64_t u = src[i], v = dst[i];
+    if (u >= 0 && u < n && v >= 0 && v < n && u != v) {
+      atomicAdd(&degc[u], 1u);
+      atomicAdd(&degc[v], 1u);
     }
   }
 }
@@ -99,17 +119,17 @@ __global__ void __launch_bounds__(kBlock) count_owned_kernel(const int32_t* __re
 // sorted keys -> col[] + rowptr[] (+ the undeduplicated row boundaries)
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool keep_entry(const uint64_t key, const uint64_t prev, bool first, int dedup, int vbits,
-                                           int64_t row_begin) {
+                                           int rshift, int64_t row_begin) {
   if (!dedup) return true;
   const uint64_t vmask = (1ull << vbits) - 1ull;
-  const int64_t row = (int64_t)(key >> vbits) + row_begin;
+  const int64_t row = (int64_t)(key >> rshift) + row_begin;
   if ((int64_t)(key & vmask) == row) return false;  // self-loop
   return first || key != prev;
 }
 
 __global__ void __launch_bounds__(kBlock) count_keep_kernel(const uint64_t* __restrict__ keys, int64_t N,
-                                                            int64_t chunk, int dedup, int vbits, int64_t row_begin,
-                                                            uint64_t* __restrict__ block_counts) {
+                                                            int64_t chunk, int dedup, int vbits, int rshift,
+                                                            int64_t row_begin, uint64_t* __restrict__ block_counts) {
   __shared__ unsigned long long total_s;
   if (threadIdx.x == 0) total_s = 0;
   __syncthreads();
@@ -118,7 +138,7 @@ __global__ void __launch_bounds__(kBlock) count_keep_kernel(const uint64_t* __re
   for (int64_t i = begin + threadIdx.x; i < end; i += kBlock) {
     const uint64_t key = keys[i];
     const uint64_t prev = i > 0 ? keys[i - 1] : 0;
-    c += keep_entry(key, prev, i == 0, dedup, vbits, row_begin);
+    c += keep_entry(key, prev, i == 0, dedup, vbits, rshift, row_begin);
   }
   for (int o = 16; o; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
   if ((threadIdx.x & 31) == 0 && c) atomicAdd(&total_s, c);
@@ -127,7 +147,8 @@ __global__ void __launch_bounds__(kBlock) count_keep_kernel(const uint64_t* __re
 }
 
 __global__ void __launch_bounds__(kBlock) compact_kernel(const uint64_t* __restrict__ keys, int64_t N, int64_t chunk,
-                                                         int dedup, int vbits, int64_t row_begin, int64_t nrows,
+                                                         int dedup, int vbits, int rshift, int64_t row_begin,
+                                                         int64_t nrows,
                                                          const uint64_t* __restrict__ block_offsets,
                                                          int32_t* __restrict__ col, int64_t* __restrict__ rowptr,
                                                          int64_t* __restrict__ orig_rowptr) {
@@ -142,7 +163,7 @@ __global__ void __launch_bounds__(kBlock) compact_kernel(const uint64_t* __restr
     const bool valid = i < end;
     const uint64_t key = valid ? keys[i] : 0;
     const uint64_t prev = (valid && i > 0) ? keys[i - 1] : 0;
-    const bool keep = valid && keep_entry(key, prev, i == 0, dedup, vbits, row_begin);
+    const bool keep = valid && keep_entry(key, prev, i == 0, dedup, vbits, rshift, row_begin);
     const unsigned b = __ballot_sync(0xffffffffu, keep);
     if (lane == 0) wtot[warp] = __popc(b);
     __syncthreads();
@@ -155,8 +176,8 @@ __global__ void __launch_bounds__(kBlock) compact_kernel(const uint64_t* __restr
     const uint64_t P = carry + before + __popc(b & lt);
     if (keep) col[P] = (int32_t)(key & vmask);
     if (valid) {
-      const int64_t row = (int64_t)(key >> vbits);
-      const int64_t prow = i > 0 ? (int64_t)(prev >> vbits) : -1;
+      const int64_t row = (int64_t)(key >> rshift);
+      const int64_t prow = i > 0 ? (int64_t)(prev >> rshift) : -1;
       for (int64_t r = prow + 1; r <= row; ++r) {  // rows (prow, row] start here; gaps are empty rows
         rowptr[r] = (int64_t)P;
         orig_rowptr[r] = i;
@@ -217,12 +238,15 @@ static int bits_for(int64_t n) {
 }
 
 Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64_t n, int64_t row_begin,
-                        int64_t row_end, bool partitioned, int dedup, int64_t nwords_override, cudaStream_t stream,
+                        int64_t row_end, bool partitioned, int dedup, int hub_first, int64_t nwords_override,
+                        cudaStream_t stream,
                         BuiltCsr* out, int64_t* launches) {
   *out = BuiltCsr();
   const int64_t nrows = row_end - row_begin;
   const int vbits = bits_for(n);
   const int rbits = bits_for(nrows > 0 ? nrows : 1);
+  const int cbits = (hub_first && vbits + rbits + 4 <= 64) ? 4 : 0;
+  const int rshift = vbits + cbits;
   const int64_t nwords = nwords_override > 0 ? nwords_override : ((nrows + 31) / 32 + 3) / 4 * 4;
   out->nrows = nrows;
   out->nwords = nwords;
@@ -255,18 +279,26 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   const int G = sort_grid_size(N);
   B2_CUDA(cudaMalloc(&scratch, sort_scratch_bytes(N) + (size_t)(G + 1) * sizeof(uint64_t)));
 
-  expand_edges_kernel<<<egrid, kBlock, 0, stream>>>(src, dst, m, n, vbits, row_begin, row_end, ka,
+  uint32_t* degc = nullptr;
+  if (cbits) {
+    B2_CUDA(cudaMalloc(&degc, (size_t)n * sizeof(uint32_t)));
+    B2_CUDA(cudaMemsetAsync(degc, 0, (size_t)n * sizeof(uint32_t), stream));
+    degree_count_kernel<<<egrid, kBlock, 0, stream>>>(src, dst, m, n, degc);
+    if (launches) *launches += 1;
+  }
+  expand_edges_kernel<<<egrid, kBlock, 0, stream>>>(src, dst, m, n, vbits, rshift, degc, row_begin, row_end, ka,
                                                     partitioned ? counters : nullptr, bad);
   if (launches) *launches += 1;
   int bad_h = 0;
   B2_CUDA(cudaMemcpyAsync(&bad_h, bad, sizeof(int), cudaMemcpyDeviceToHost, stream));
   B2_CUDA(cudaStreamSynchronize(stream));
+  cudaFree(degc);
   if (bad_h) {
     cudaFree(ka); cudaFree(kb); cudaFree(scratch); cudaFree(counters); cudaFree(bad);
     return make_error(B2BFS_ERR_RANGE, "edge list holds a vertex id outside [0, vertex_num)");
   }
 
-  B2_TRY(radix_sort_u64(ka, kb, N, vbits + rbits, scratch, stream, &sorted, launches));
+  B2_TRY(radix_sort_u64(ka, kb, N, rshift + rbits, scratch, stream, &sorted, launches));
 
   // chunked two-pass compaction over the sorted keys
   int64_t chunk = (N + G - 1) / G;
@@ -274,7 +306,7 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   if (chunk == 0) chunk = kBlock;
   uint64_t* block_counts = reinterpret_cast<uint64_t*>(scratch);
   uint64_t* total_d = block_counts + G;
-  count_keep_kernel<<<G, kBlock, 0, stream>>>(sorted, N, chunk, dedup, vbits, row_begin, block_counts);
+  count_keep_kernel<<<G, kBlock, 0, stream>>>(sorted, N, chunk, dedup, vbits, rshift, row_begin, block_counts);
   scan_u64_single_block<<<1, 1024, 0, stream>>>(block_counts, G, total_d);
   uint64_t entries = 0;
   B2_CUDA(cudaMemcpyAsync(&entries, total_d, sizeof(entries), cudaMemcpyDeviceToHost, stream));
@@ -297,7 +329,7 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
     B2_CUDA(cudaMemsetAsync(out->rowptr, 0, (size_t)(nrows + 1) * sizeof(int64_t), stream));
     B2_CUDA(cudaMemsetAsync(orig_rowptr, 0, (size_t)(nrows + 1) * sizeof(int64_t), stream));
   } else {
-    compact_kernel<<<G, kBlock, 0, stream>>>(sorted, N, chunk, dedup, vbits, row_begin, nrows, block_counts,
+    compact_kernel<<<G, kBlock, 0, stream>>>(sorted, N, chunk, dedup, vbits, rshift, row_begin, nrows, block_counts,
                                              out->col, out->rowptr, orig_rowptr);
     if (launches) *launches += 1;
   }

@@ -81,7 +81,10 @@ int b2bfs_comm_unique_id(void* out128);
 
 /* Options, set before loading a graph unless stated: "dedup" (1: drop duplicate entries and
  * self-loops while building the CSR — depths do not change; 0: keep the reference's multigraph,
- * bfs.cu:860-861), "mode", "engine" (both may change between searches), "alpha", "beta" (switch
+ * bfs.cu:860-861), "hub_first" (1: inside a row neighbours are ordered by descending
+ * floor(log2 degree), then ascending id, so that bottom-up meets a hub first; 0: ascending id),
+ * "multi_engine" (multi-rank: 0 peer-memory kernel, 1 NCCL per level), "mode", "engine" (these
+ * three may change between searches), "alpha", "beta" (switch
  * heuristic), "keep_edges" (1: keep the input tuples resident for b2bfs_copy_edges).
  * Replaces the reference's compile-time switches (#define DeviceNum, commented call sites in main,
  * bfs.cu:19, 805-819). */

@@ -57,7 +57,8 @@ def test_device_generator_is_the_host_generator(b2, gpu, kind, scale, ef, seed):
 @pytest.mark.parametrize("kind,scale", [(0, 11), (1, 10), (2, 8)])
 def test_csr_build_matches_reference_rows(b2, kind, scale, dedup):
     """Row CONTENT equals the reference's rows (bfs.cu:851-875) as multisets (dedup=0) or as sets
-    without self-loops (dedup=1); within-row order is ours (ascending), which no depth depends on."""
+    without self-loops (dedup=1); within-row order is ours (hubs first: descending floor(log2 degree),
+    then ascending id), which no depth depends on."""
     n, s, d = oracle.generate_edges(kind, scale, 16, 3)
     g = oracle.build_csr(n, s, d)
     with b2.Bfs(0, dedup=dedup) as h:
@@ -66,11 +67,16 @@ def test_csr_build_matches_reference_rows(b2, kind, scale, dedup):
         assert np.array_equal(h.degrees(), g.sizes)  # the reference's edgesSize[]
         assert rowptr[0] == 0 and rowptr[-1] == len(col) == h.csr_entries
         assert np.all(np.diff(rowptr) >= 0)
+        nl = np.bincount(s[s != d], minlength=n) + np.bincount(d[s != d], minlength=n)
+        cls = np.floor(np.log2(np.maximum(nl, 1))).astype(np.int64).clip(0, 15)
         for v in range(n):
             ref_row = np.sort(g.adj[g.offsets[v]:g.offsets[v] + g.sizes[v]])
             if dedup:
                 ref_row = np.unique(ref_row[ref_row != v])
-            assert np.array_equal(col[rowptr[v]:rowptr[v + 1]], ref_row), f"row {v}"
+            row = col[rowptr[v]:rowptr[v + 1]]
+            assert np.array_equal(np.sort(row), ref_row), f"row {v}"
+            key = (15 - cls[row]) * (1 << 32) + row  # hub-first order: class descending, then id ascending
+            assert np.all(np.diff(key) >= 0), f"row {v} order"
 
 
 @pytest.mark.parametrize("name", golden_names())
