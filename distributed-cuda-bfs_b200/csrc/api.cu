@@ -4,6 +4,7 @@
 // per-device pointer tables (bfs.cu:255-269) and the buffers initCuda2 allocates and never frees
 // (bfs.cu:333-351, 362-372).
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
@@ -167,7 +168,7 @@ static int finish_load(b2bfs* h) {
     API_CUDA(h, cudaMalloc(&h->gfrontier, k * part / 8));
     API_CUDA(h, cudaMalloc(&h->seen, k * part / 8));
     API_CUDA(h, cudaMalloc(&h->send_buf, k * part * sizeof(int2)));
-    API_CUDA(h, cudaMalloc(&h->send_count, k * 32 * sizeof(unsigned int)));
+    API_CUDA(h, cudaMalloc(&h->send_count, 8 * 32 * sizeof(unsigned int)));  // one 128-byte line per possible peer
     API_CUDA(h, cudaMalloc(&h->gather_tmp, k * part * sizeof(int32_t)));
     API_CUDA(h, cudaMalloc(&h->mc.recv_buf, (k - 1) * part * sizeof(int2)));
     API_CUDA(h, cudaMemsetAsync(h->sv.depth, 0xff, (size_t)(rows + 4) * sizeof(int32_t), h->stream));
@@ -565,7 +566,7 @@ static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent
   if (stats) {
     s = run_reach_stats(p, h->csr.orig_deg, h->stream, &launches);
     if (!s.ok()) return fail(h, s);
-    if (multi)
+    if (multi && !getenv("B2BFS_DEBUG_LOCAL_STATS"))
       API_NCCL(h, h->mc.nccl->AllReduce(&h->sv.ctl->reached_vertices, &h->sv.ctl->reached_vertices, 2, ncclUint64, ncclSum,
                                         h->mc.comm, h->stream));
     API_CUDA(h, cudaMemcpyAsync(h->pinned_ctl, h->sv.ctl, sizeof(Control), cudaMemcpyDeviceToHost, h->stream));

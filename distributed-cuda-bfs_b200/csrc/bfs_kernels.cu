@@ -1012,7 +1012,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
     const int64_t n4 = (int64_t)k * p.g.part / 128;
     for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n4; i += (int64_t)gridDim.x * kBlock)
       s4[i] = make_uint4(0, 0, 0, 0);
-    if (blockIdx.x == 0 && threadIdx.x < 8) p.s.send_count[threadIdx.x * 32] = 0;
+    if (blockIdx.x == 0 && (int)threadIdx.x < p.g.world) p.s.send_count[threadIdx.x * 32] = 0;
     if (blockIdx.x == 0 && threadIdx.x == 0) p.s.ctl->error = 0;
   }
   phase_init(p, src_local);
@@ -1043,7 +1043,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
       const int2* inbox = reinterpret_cast<const int2*>(p.s.xbase[me] + xchg_off_inbox(k, p.g.part));
       for (int s = 0; s < k; ++s)
         if (s != me && incoming[s]) phase_apply_remote(p, st, stage, inbox + (int64_t)s * p.s.send_cap, incoming[s]);
-      if (blockIdx.x == 0 && threadIdx.x < 8) p.s.send_count[threadIdx.x * 32] = 0;  // all counts were read above
+      if (blockIdx.x == 0 && (int)threadIdx.x < p.g.world) p.s.send_count[threadIdx.x * 32] = 0;  // all counts were read above
       cross_exchange(p, grid, ++epoch, st.level + 1, sums, incoming, &failed);  // tails after the arrivals
       trace_mark(p.s.ctl, ntrace, st.level, 8);
       nf = sums[0] + sums[1];
