@@ -418,10 +418,10 @@ __device__ __forceinline__ void phase_apply_remote(const BfsParams& p, const Loo
   for (int64_t r = 0; r < rounds; ++r) {  // warp-uniform trip count
     const int64_t i = r * nthreads + (int64_t)blockIdx.x * kBlock + threadIdx.x;
     if (i < count) {
-      const int2 e = recv[i];
+      const int2 e = __ldcg(recv + i);  // written by another GPU (or by NCCL): read at L2
       const int32_t vl = e.x - (int32_t)p.g.vbase;
       const uint32_t w = (uint32_t)vl >> 5, bit = 1u << (vl & 31);
-      if (!(p.s.visited[w] & bit) && !(atomicOr(&p.s.visited[w], bit) & bit)) {
+      if ((uint32_t)vl < (uint32_t)p.g.n && !(p.s.visited[w] & bit) && !(atomicOr(&p.s.visited[w], bit) & bit)) {
         p.s.depth[vl] = level + 1;
         p.s.parent[vl] = e.y;
         const int64_t d = __ldg(p.g.rowptr + vl + 1) - __ldg(p.g.rowptr + vl);
@@ -939,7 +939,7 @@ __device__ __forceinline__ unsigned long long global_ns() {
 __device__ __forceinline__ volatile unsigned long long* xrecord(const BfsParams& p, int on_rank, unsigned long long epoch,
                                                                 int from_rank) {
   return reinterpret_cast<volatile unsigned long long*>(p.s.xbase[on_rank] + xchg_off_records(p.g.world, p.g.part)) +
-         ((epoch & 3) * 8 + from_rank) * 16;
+         ((epoch & 3) * 8 + from_rank) * 32;
 }
 
 // All ranks call this the same number of times.  On return sums[0..4] = totals over ranks of
@@ -949,7 +949,10 @@ __device__ __forceinline__ void cross_exchange(const BfsParams& p, cg::grid_grou
                                                unsigned long long* sums, unsigned int* incoming, int* failed) {
   __shared__ unsigned long long rec_s[8][16];
   const int k = p.g.world, me = p.g.rank;
-  grid.sync();  // everything this GPU wrote for its peers during the phase has been issued
+  // every thread drains ITS OWN stores to peer memory before it arrives: a fence issued later by one
+  // thread of CTA 0 is not known to wait for other SMs' writes still in flight on other NVLink lanes
+  __threadfence_system();
+  grid.sync();  // everything this GPU wrote for its peers during the phase has landed
   if (blockIdx.x == 0 && (int)threadIdx.x < k) {
     const int d = threadIdx.x;
     const LevelSlot* s = &p.s.ctl->slot[slot & 3];
@@ -962,10 +965,10 @@ __device__ __forceinline__ void cross_exchange(const BfsParams& p, cg::grid_grou
     dst[4] = (unsigned long long)p.s.ctl->src_degree;
     for (int j = 0; j < 8; ++j) dst[8 + j] = j < k ? ld_volatile(&p.s.send_count[j * 32]) : 0u;
     __threadfence_system();
-    dst[15] = epoch;  // arrival flag, after the payload
+    dst[31] = epoch;  // arrival flag, after the payload
     volatile unsigned long long* src = xrecord(p, me, epoch, d);
     const unsigned long long t0 = global_ns();
-    while (src[15] != epoch) {
+    while (src[31] != epoch) {
       if (global_ns() - t0 > 4000000000ull) {  // 4 s: a peer died or never launched
         p.s.ctl->error = 1;
         break;
@@ -974,6 +977,8 @@ __device__ __forceinline__ void cross_exchange(const BfsParams& p, cg::grid_grou
     __threadfence_system();
   }
   grid.sync();  // the records of every rank are in this GPU's memory
+  if (threadIdx.x == 0) __threadfence();  // drop L1 lines that predate what the peers just wrote here
+  __syncthreads();
   if ((int)threadIdx.x < k * 16) rec_s[threadIdx.x >> 4][threadIdx.x & 15] = xrecord(p, me, epoch, threadIdx.x >> 4)[threadIdx.x & 15];
   __syncthreads();
   for (int i = 0; i < 5; ++i) sums[i] = 0;

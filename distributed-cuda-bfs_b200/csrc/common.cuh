@@ -132,7 +132,8 @@ struct SearchView {
   // IPC; all nullptr when exchanges go through NCCL.  Layout of a region (same on every rank):
   //   [2][world * part/8 B]  frontier bitmaps, ping-pong
   //   [world][part] int2     inbox: bucket s holds the (vertex, parent) pairs rank s found for me
-  //   [4][8][16] u64         per-exchange records of every rank, word 15 = epoch (the arrival flag)
+  //   [4][8][32] u64         per-exchange records of every rank: words 0-4 counters, 8-15 pair counts
+  //                          per peer, word 31 = epoch (the arrival flag, written last)
   unsigned char* xbase[8];
 };
 
@@ -142,7 +143,7 @@ __host__ __device__ inline size_t xchg_off_records(int world, int64_t part) {
   return xchg_off_inbox(world, part) + (size_t)world * (size_t)part * sizeof(int2);
 }
 __host__ __device__ inline size_t xchg_region_bytes(int world, int64_t part) {
-  return xchg_off_records(world, part) + 4 * 8 * 16 * sizeof(unsigned long long);
+  return xchg_off_records(world, part) + 4 * 8 * 32 * sizeof(unsigned long long);
 }
 
 struct Tuning {
