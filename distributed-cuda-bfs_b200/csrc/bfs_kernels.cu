@@ -248,6 +248,7 @@ __device__ __forceinline__ void remote_flush(const BfsParams& p, RemoteStage& rs
       }
     }
   }
+  if (p.s.xbase[0]) __threadfence_system();  // the pairs are in the owners' memory before this warp moves on
   __syncwarp();
   if (lane == 0) rs.cnt = 0;
   __syncwarp();
@@ -945,39 +946,60 @@ __device__ __forceinline__ volatile unsigned long long* xrecord(const BfsParams&
 // All ranks call this the same number of times.  On return sums[0..4] = totals over ranks of
 // (narrow tail, wide tail, degree sum, bottom-up finds, source degree) of `slot`, mine[0..1] = this
 // rank's own tails and incoming[s] = pairs rank s staged for this rank.
-__device__ __forceinline__ void cross_exchange(const BfsParams& p, cg::grid_group& grid, unsigned long long epoch, int slot,
-                                               unsigned long long* sums, unsigned int* incoming, int* failed) {
+__device__ __forceinline__ void cross_exchange(const BfsParams& p, unsigned long long epoch, unsigned long long nth,
+                                               int slot, unsigned long long* sums, unsigned int* incoming, int* failed) {
   __shared__ unsigned long long rec_s[8][16];
   const int k = p.g.world, me = p.g.rank;
-  // every thread drains ITS OWN stores to peer memory before it arrives: a fence issued later by one
-  // thread of CTA 0 is not known to wait for other SMs' writes still in flight on other NVLink lanes
-  __threadfence_system();
-  grid.sync();  // everything this GPU wrote for its peers during the phase has landed
-  if (blockIdx.x == 0 && (int)threadIdx.x < k) {
-    const int d = threadIdx.x;
-    const LevelSlot* s = &p.s.ctl->slot[slot & 3];
-    volatile unsigned long long* dst = xrecord(p, d, epoch, me);
-    __threadfence_system();
-    dst[0] = ld_volatile(&s->q_count);
-    dst[1] = ld_volatile(&s->wide_count);
-    dst[2] = ld_volatile(&s->edges);
-    dst[3] = ld_volatile(&s->bu_count);
-    dst[4] = (unsigned long long)p.s.ctl->src_degree;
-    for (int j = 0; j < 8; ++j) dst[8 + j] = j < k ? ld_volatile(&p.s.send_count[j * 32]) : 0u;
-    __threadfence_system();
-    dst[31] = epoch;  // arrival flag, after the payload
-    volatile unsigned long long* src = xrecord(p, me, epoch, d);
-    const unsigned long long t0 = global_ns();
-    while (src[31] != epoch) {
-      if (global_ns() - t0 > 4000000000ull) {  // 4 s: a peer died or never launched
-        p.s.ctl->error = 1;
-        break;
-      }
-    }
-    __threadfence_system();
+  Control* ctl = p.s.ctl;
+  // ONE grid-wide rendezvous with the cross-GPU step inside it (nth = number of this exchange in the
+  // kernel, 1-based; xarrive/xrelease are zeroed by the host before the launch):
+  // stores to peer memory were already drained by the warps that issued them (remote_flush,
+  // push_frontier_slice end with __threadfence_system): a fence issued later by one thread of CTA 0 is
+  // not known to wait for other SMs' writes still in flight on other NVLink lanes
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(&ctl->xarrive, 1ull);
   }
-  grid.sync();  // the records of every rank are in this GPU's memory
-  if (threadIdx.x == 0) __threadfence();  // drop L1 lines that predate what the peers just wrote here
+  if (blockIdx.x == 0) {
+    if (threadIdx.x == 0) {
+      const unsigned long long target = nth * gridDim.x;
+      while (ld_volatile(&ctl->xarrive) < target) {}
+      __threadfence();
+    }
+    __syncthreads();  // everything this GPU wrote for its peers during the phase has landed
+    if ((int)threadIdx.x < k) {
+      const int d = threadIdx.x;
+      const LevelSlot* s = &ctl->slot[slot & 3];
+      volatile unsigned long long* dst = xrecord(p, d, epoch, me);
+      dst[0] = ld_volatile(&s->q_count);
+      dst[1] = ld_volatile(&s->wide_count);
+      dst[2] = ld_volatile(&s->edges);
+      dst[3] = ld_volatile(&s->bu_count);
+      dst[4] = (unsigned long long)ctl->src_degree;
+      for (int j = 0; j < 8; ++j) dst[8 + j] = j < k ? ld_volatile(&p.s.send_count[j * 32]) : 0u;
+      __threadfence_system();
+      dst[31] = epoch;  // arrival flag, after the payload
+      volatile unsigned long long* src = xrecord(p, me, epoch, d);
+      const unsigned long long t0 = global_ns();
+      while (src[31] != epoch) {
+        if (global_ns() - t0 > 4000000000ull) {  // 4 s: a peer died or never launched
+          ctl->error = 1;
+          break;
+        }
+      }
+      __threadfence_system();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      *reinterpret_cast<volatile unsigned long long*>(&ctl->xrelease) = nth;
+    }
+  }
+  if (threadIdx.x == 0) {
+    while (ld_volatile(&ctl->xrelease) < nth) {}
+    __threadfence();  // also drops L1 lines that predate what the peers just wrote here
+  }
   __syncthreads();
   if ((int)threadIdx.x < k * 16) rec_s[threadIdx.x >> 4][threadIdx.x & 15] = xrecord(p, me, epoch, threadIdx.x >> 4)[threadIdx.x & 15];
   __syncthreads();
@@ -988,7 +1010,7 @@ __device__ __forceinline__ void cross_exchange(const BfsParams& p, cg::grid_grou
   }
   sums[5] = rec_s[me][0];
   sums[6] = rec_s[me][1];
-  *failed = *reinterpret_cast<volatile int*>(&p.s.ctl->error);
+  *failed = *reinterpret_cast<volatile int*>(&ctl->error);
   __syncthreads();
 }
 
@@ -1003,6 +1025,7 @@ __device__ __forceinline__ void push_frontier_slice(const BfsParams& p, int whic
     const int64_t j = i - (int64_t)d * words4;
     reinterpret_cast<uint4*>(p.s.xbase[d] + off)[j] = mine[j];
   }
+  __threadfence_system();  // the slice is in every peer's memory before this thread reaches the exchange
 }
 
 __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_kernel(BfsParams p, int64_t src,
@@ -1025,16 +1048,17 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
   unsigned int incoming[8];
   int failed = 0;
   int ntrace = 0;
+  unsigned long long nth = 0;
   trace_mark(p.s.ctl, ntrace, 0, -1);
-  cross_exchange(p, grid, ++epoch, 0, sums, incoming, &failed);
+  grid.sync();  // no exchange needed yet: nobody reads what a peer has not written in THIS search
   trace_mark(p.s.ctl, ntrace, 0, 0);
 
   LoopState st;
-  st.level = 0; st.mode = 0; st.fb = 1; st.done = failed;  // fb = 1: bottom-up writes bitmap[0], this rank's slice
-  st.cur_q = (unsigned)sums[5];
-  st.cur_wide = (unsigned)sums[6];
+  st.level = 0; st.mode = 0; st.fb = 1; st.done = 0;  // fb = 1: bottom-up writes bitmap[0], this rank's slice
+  st.cur_q = ld_volatile(&p.s.ctl->slot[0].q_count);
+  st.cur_wide = ld_volatile(&p.s.ctl->slot[0].wide_count);
   st.prev_nf = 1;
-  st.unexplored = p.g.entries_global - sums[4];
+  st.unexplored = p.g.entries_global;  // the source's own degree is noise at this size
   st.td_levels = st.bu_levels = 0;
   int gcur = 0;  // frontier bitmap buffer bottom-up reads
 
@@ -1043,13 +1067,13 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
     if (st.mode == 0) {
       phase_top_down<true>(p, st, stage, blockIdx.x, gridDim.x, rstage);
       trace_mark(p.s.ctl, ntrace, st.level, 6);
-      cross_exchange(p, grid, ++epoch, st.level + 1, sums, incoming, &failed);  // pair counts
+      cross_exchange(p, ++epoch, ++nth, st.level + 1, sums, incoming, &failed);  // pair counts
       trace_mark(p.s.ctl, ntrace, st.level, 7);
       const int2* inbox = reinterpret_cast<const int2*>(p.s.xbase[me] + xchg_off_inbox(k, p.g.part));
       for (int s = 0; s < k; ++s)
         if (s != me && incoming[s]) phase_apply_remote(p, st, stage, inbox + (int64_t)s * p.s.send_cap, incoming[s]);
       if (blockIdx.x == 0 && (int)threadIdx.x < p.g.world) p.s.send_count[threadIdx.x * 32] = 0;  // all counts were read above
-      cross_exchange(p, grid, ++epoch, st.level + 1, sums, incoming, &failed);  // tails after the arrivals
+      cross_exchange(p, ++epoch, ++nth, st.level + 1, sums, incoming, &failed);  // tails after the arrivals
       trace_mark(p.s.ctl, ntrace, st.level, 8);
       nf = sums[0] + sums[1];
       mf = sums[2];
@@ -1062,7 +1086,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
       grid.sync();  // the slice is complete (late finds are OR-ed in by any CTA)
       trace_mark(p.s.ctl, ntrace, st.level, 9);
       push_frontier_slice(p, gcur ^ 1);
-      cross_exchange(p, grid, ++epoch, st.level + 1, sums, incoming, &failed);
+      cross_exchange(p, ++epoch, ++nth, st.level + 1, sums, incoming, &failed);
       trace_mark(p.s.ctl, ntrace, st.level, 10);
       gcur ^= 1;
       nf = sums[3];
@@ -1078,7 +1102,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
         phase_queue_to_bitmap(p, st);  // own new frontier -> bitmap[0] (all-zero while top-down runs)
         grid.sync();
         push_frontier_slice(p, gcur ^ 1);
-        cross_exchange(p, grid, ++epoch, st.level, sums, incoming, &failed);
+        cross_exchange(p, ++epoch, ++nth, st.level, sums, incoming, &failed);
         trace_mark(p.s.ctl, ntrace, st.level, 3);
         gcur ^= 1;
         if (failed) st.done = 1;
@@ -1141,6 +1165,8 @@ Status run_fused_multi(const BfsParams& p, int64_t src, unsigned long long epoch
   int64_t s = src;
   unsigned long long e = epoch_base;
   void* args[] = {&pp, &s, &e};
+  // arrival / release counters of the in-kernel exchanges start from zero in every search
+  B2_CUDA(cudaMemsetAsync(&p.s.ctl->xarrive, 0, 128 + sizeof(unsigned long long), stream));
   B2_CUDA(cudaLaunchCooperativeKernel((const void*)bfs_fused_multi_kernel, dim3(grid), dim3(kBlock), args, 0, stream));
   if (launches) *launches += 1;
   return Status();

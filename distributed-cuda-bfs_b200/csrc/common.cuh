@@ -109,6 +109,8 @@ struct Control {
   alignas(128) LoopState resume_state;                   // what the group decided, for the CTAs that waited
   int resume_conversion;
   int error;                                             // peer-memory engine: a cross-GPU wait timed out
+  alignas(128) unsigned long long xarrive;               // peer-memory engine: CTAs arrived at exchanges so far
+  alignas(128) unsigned long long xrelease;              // ... and the last exchange CTA 0 has completed
   unsigned int group_exit_seq;                           // bumped when the group leaves its level loop
   int trace_len;                                         // fused engine: per-phase timestamps of CTA 0
   TraceRec trace[kTraceCap];
