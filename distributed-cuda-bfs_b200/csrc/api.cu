@@ -566,7 +566,7 @@ static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent
   if (stats) {
     s = run_reach_stats(p, h->csr.orig_deg, h->stream, &launches);
     if (!s.ok()) return fail(h, s);
-    if (multi && !getenv("B2BFS_DEBUG_LOCAL_STATS"))
+    if (multi)
       API_NCCL(h, h->mc.nccl->AllReduce(&h->sv.ctl->reached_vertices, &h->sv.ctl->reached_vertices, 2, ncclUint64, ncclSum,
                                         h->mc.comm, h->stream));
     API_CUDA(h, cudaMemcpyAsync(h->pinned_ctl, h->sv.ctl, sizeof(Control), cudaMemcpyDeviceToHost, h->stream));

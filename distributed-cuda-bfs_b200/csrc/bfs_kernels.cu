@@ -93,7 +93,14 @@ __device__ __forceinline__ void stage_flush(WarpStage& sg, LevelSlot* ns, int32_
     if (lane == 0) sg.ncnt = 0;
   }
   if (wc >= kStageFlush || (force && wc > 0)) {
-    for (int i0 = 0; i0 < wc; i0 += 32) {  // one tail atomic per 32 staged rows
+    // one tail atomic for everything staged: total first, then per-round prefixes from a running base
+    unsigned mine = 0;
+    for (int i = lane; i < wc; i += 32) mine += (unsigned)sg.witems[i];
+    for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+    unsigned run = 0;
+    if (lane == 0) run = atomicAdd(&ns->wide_count, mine);
+    run = __shfl_sync(0xffffffffu, run, 0);
+    for (int i0 = 0; i0 < wc; i0 += 32) {
       const int i = i0 + (int)lane;
       const unsigned items = i < wc ? (unsigned)sg.witems[i] : 0u;
       const int32_t v = i < wc ? sg.wide[i] : 0;
@@ -102,9 +109,8 @@ __device__ __forceinline__ void stage_flush(WarpStage& sg, LevelSlot* ns, int32_
         const unsigned y = __shfl_up_sync(0xffffffffu, incl, o);
         if (lane >= (unsigned)o) incl += y;
       }
-      unsigned base = 0;
-      if (lane == 31) base = atomicAdd(&ns->wide_count, incl);
-      base = __shfl_sync(0xffffffffu, base, 31) + incl - items;
+      const unsigned base = run + incl - items;
+      run += __shfl_sync(0xffffffffu, incl, 31);
       if (items && items <= 8) {
         for (unsigned c = 0; c < items; ++c) nwq[base + c] = make_int2(v, (int)c);
       }

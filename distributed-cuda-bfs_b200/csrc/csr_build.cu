@@ -231,6 +231,21 @@ __global__ void __launch_bounds__(kBlock) finish_rows_kernel(int64_t nrows, int6
   if (lane == 0 && mx) atomicMax(max_degree, mx);
 }
 
+// temporaries of one build: freed on every exit path
+struct DeviceTemps {
+  void* ptrs[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  int count = 0;
+  template <typename T>
+  cudaError_t alloc(T** p, size_t bytes) {
+    const cudaError_t e = cudaMalloc(p, bytes);
+    if (e == cudaSuccess && count < 8) ptrs[count++] = *p;
+    return e;
+  }
+  ~DeviceTemps() {
+    for (int i = 0; i < count; ++i) cudaFree(ptrs[i]);
+  }
+};
+
 static int bits_for(int64_t n) {
   int b = 1;
   while (((int64_t)1 << b) < n) ++b;
@@ -253,8 +268,9 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
 
   unsigned long long* counters = nullptr;  // [0] append cursor / owned total, [1] wide items, [2] max degree
   int* bad = nullptr;
-  B2_CUDA(cudaMalloc(&counters, 4 * sizeof(unsigned long long)));
-  B2_CUDA(cudaMalloc(&bad, sizeof(int)));
+  DeviceTemps temps;
+  B2_CUDA(temps.alloc(&counters, 4 * sizeof(unsigned long long)));
+  B2_CUDA(temps.alloc(&bad, sizeof(int)));
   B2_CUDA(cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), stream));
   B2_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), stream));
 
@@ -274,14 +290,14 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   uint64_t *ka = nullptr, *kb = nullptr, *sorted = nullptr;
   void* scratch = nullptr;
   const size_t kbytes = (size_t)(N > 0 ? N : 1) * sizeof(uint64_t);
-  B2_CUDA(cudaMalloc(&ka, kbytes));
-  B2_CUDA(cudaMalloc(&kb, kbytes));
+  B2_CUDA(temps.alloc(&ka, kbytes));
+  B2_CUDA(temps.alloc(&kb, kbytes));
   const int G = sort_grid_size(N);
-  B2_CUDA(cudaMalloc(&scratch, sort_scratch_bytes(N) + (size_t)(G + 1) * sizeof(uint64_t)));
+  B2_CUDA(temps.alloc(&scratch, sort_scratch_bytes(N) + (size_t)(G + 1) * sizeof(uint64_t)));
 
   uint32_t* degc = nullptr;
   if (cbits) {
-    B2_CUDA(cudaMalloc(&degc, (size_t)n * sizeof(uint32_t)));
+    B2_CUDA(temps.alloc(&degc, (size_t)n * sizeof(uint32_t)));
     B2_CUDA(cudaMemsetAsync(degc, 0, (size_t)n * sizeof(uint32_t), stream));
     degree_count_kernel<<<egrid, kBlock, 0, stream>>>(src, dst, m, n, degc);
     if (launches) *launches += 1;
@@ -292,9 +308,7 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   int bad_h = 0;
   B2_CUDA(cudaMemcpyAsync(&bad_h, bad, sizeof(int), cudaMemcpyDeviceToHost, stream));
   B2_CUDA(cudaStreamSynchronize(stream));
-  cudaFree(degc);
   if (bad_h) {
-    cudaFree(ka); cudaFree(kb); cudaFree(scratch); cudaFree(counters); cudaFree(bad);
     return make_error(B2BFS_ERR_RANGE, "edge list holds a vertex id outside [0, vertex_num)");
   }
 
@@ -317,7 +331,7 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   out->orig_entries = N;
   int64_t* orig_rowptr = nullptr;
   B2_CUDA(cudaMalloc(&out->rowptr, (size_t)(nrows + 1) * sizeof(int64_t)));
-  B2_CUDA(cudaMalloc(&orig_rowptr, (size_t)(nrows + 1) * sizeof(int64_t)));
+  B2_CUDA(temps.alloc(&orig_rowptr, (size_t)(nrows + 1) * sizeof(int64_t)));
   // col is read in 16-byte vectors and 16-byte-aligned bulk copies: pad both ends
   B2_CUDA(cudaMalloc(&out->col, ((size_t)entries + 64) * sizeof(int32_t)));
   B2_CUDA(cudaMalloc(&out->orig_deg, (size_t)nwords * 32 * sizeof(uint32_t)));
@@ -345,12 +359,6 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   out->wide_items = (int64_t)hc[0];
   out->max_degree = (int64_t)hc[1];
 
-  cudaFree(orig_rowptr);
-  cudaFree(ka);
-  cudaFree(kb);
-  cudaFree(scratch);
-  cudaFree(counters);
-  cudaFree(bad);
   return Status();
 }
 
