@@ -102,7 +102,7 @@ def lib() -> C.CDLL:
 
 
 NOALLOC_MAX_VERTICES = 262144
-NOALLOC_MAX_ENTRIES = 16777216
+NOALLOC_MAX_ENTRIES = 8388608
 
 
 def search_noalloc(device: int, n: int, entries: int, rowptr_ptr: int, col_ptr: int, src: int, depth_ptr: int,

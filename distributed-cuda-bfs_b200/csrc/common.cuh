@@ -15,7 +15,7 @@ constexpr int kBlock = 256;              // threads per CTA for every kernel in 
 constexpr int kWarpsPerBlock = kBlock / 32;
 constexpr int kSMs = 148;                // B200: 2 dies x 74 SMs; grids are sized in multiples of it
 constexpr int kNarrow = 32;              // rows narrower than this are gathered 32 at a time by one warp
-constexpr int kChunk = 256;              // wider rows are cut into work items of this many entries
+constexpr int kChunk = 128;              // wider rows are cut into work items of this many entries
 
 // ---------------------------------------------------------------------------------------------
 // error plumbing: every CUDA call is checked (the reference discards all return codes, bfs.cu:336)

@@ -162,7 +162,7 @@ int b2bfs_last_trace(b2bfs_t* h, int32_t* level_out, int32_t* phase_out, double*
  * at zero), so two searches overlapping on the GPU would corrupt each other: the library takes a
  * host lock and returns only when the search is complete, which keeps its own calls apart. */
 #define B2BFS_NOALLOC_MAX_VERTICES 262144   /* 2^18 */
-#define B2BFS_NOALLOC_MAX_ENTRIES 16777216  /* 2^24 directed CSR entries */
+#define B2BFS_NOALLOC_MAX_ENTRIES 8388608   /* 2^23 directed CSR entries */
 int b2bfs_search_noalloc(int device, int64_t n, int64_t entries, const int64_t* rowptr_dev, const int32_t* col_dev,
                          int64_t src, int32_t* depth_dev, int32_t* parent_dev, void* cuda_stream,
                          int32_t* levels_out);
