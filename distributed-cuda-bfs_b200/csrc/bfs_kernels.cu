@@ -267,7 +267,7 @@ __device__ __forceinline__ void remote_flush(const BfsParams& p, RemoteStage& rs
 template <bool kMulti>
 __device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpStage& sg, RemoteStage* rs,
                                           const int32_t (&v)[4], const int32_t (&u)[4], const bool (&valid)[4],
-                                          unsigned long long& edges_acc) {
+                                          unsigned long long& edges_acc, bool mark) {
   uint32_t word[4];
   bool c[4], local[4];
   int32_t vl[4];
@@ -307,6 +307,9 @@ __device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpSta
         p.s.parent[vl[k]] = u[k];
         edges_acc += (unsigned long long)d[k];
         route_vertex(sg, vl[k], d[k]);
+        // the next level will most likely run bottom-up: leave the frontier bit behind now and
+        // save the queue->bitmap pass and its grid-wide barrier
+        if (mark) atomicOr(&p.s.bitmap[0][(uint32_t)vl[k] >> 5], 1u << (vl[k] & 31));
       } else if (kMulti) {
         rs->pair[atomicAdd(&rs->cnt, 1)] = make_int2(v[k], u[k]);
       }
@@ -316,7 +319,7 @@ __device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpSta
 
 template <bool kMulti>
 __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStage* stage, int bid, int nb,
-                                               RemoteStage* rstage = nullptr) {
+                                               RemoteStage* rstage = nullptr, bool mark = false) {
   const int level = st.level;
   const int32_t* q = p.s.queue[level & 1];
   const int2* wq = p.s.wideq[level & 1];
@@ -378,7 +381,7 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
           valid[j] = k < total;
           v[j] = valid[j] ? __ldg(p.g.col + ors + (k - oe)) : 0;
         }
-        td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc);
+        td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark);
         stage_flush(sg, ns, nq, nwq, false);
         if (kMulti) remote_flush(p, *rst, false);
       }
@@ -396,7 +399,7 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
           const int32_t uu[4] = {u + vbase, u + vbase, u + vbase, u + vbase};
           const bool valid[4] = {base >= rs, base + 1 >= rs && base + 1 < re, base + 2 >= rs && base + 2 < re,
                                  base + 3 >= rs && base + 3 < re};
-          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc);
+          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark);
         }
         stage_flush(sg, ns, nq, nwq, false);
         if (kMulti) remote_flush(p, *rst, false);
@@ -691,6 +694,20 @@ __device__ __forceinline__ void phase_queue_to_bitmap(const BfsParams& p, const 
   }
 }
 
+// take back the frontier bits a "marking" top-down level left in bitmap[0] when the search stays
+// top-down after all (the bitmaps must be all-zero while top-down runs)
+__device__ __forceinline__ void phase_unmark(const BfsParams& p, const LoopState& st) {
+  const int32_t* q = p.s.queue[st.level & 1];
+  const int2* wq = p.s.wideq[st.level & 1];
+  uint32_t* bm = p.s.bitmap[0];
+  const int64_t tid = (int64_t)blockIdx.x * kBlock + threadIdx.x, nthreads = (int64_t)gridDim.x * kBlock;
+  for (int64_t i = tid; i < (int64_t)st.cur_q; i += nthreads) bm[(uint32_t)__ldcg(q + i) >> 5] = 0;
+  for (int64_t i = tid; i < (int64_t)st.cur_wide; i += nthreads) {
+    const int2 it = __ldcg(wq + i);
+    if (it.y == 0) bm[(uint32_t)it.x >> 5] = 0;
+  }
+}
+
 // next bitmap (written by the bottom-up level that just ended) -> work lists of level st.level,
 // routed by degree through the same per-warp staging; clears both bitmaps so the "all-zero while
 // top-down" invariant holds again
@@ -864,6 +881,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
   trace_mark(p.s.ctl, ntrace, 0, 0);
   while (!st.done) {
     Conversion cv = kNoConversion;
+    bool marked = false;
     if (st.mode == 0 && frontier_work(st) <= kGroupMaxWork) {
       ++group_seq;
       if ((int)blockIdx.x < group) {
@@ -898,7 +916,9 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
       trace_mark(p.s.ctl, ntrace, st.level, 5);
     } else {
       const int ph = st.mode == 0 ? 1 : 2;
-      if (st.mode == 0) phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x); else phase_bottom_up(p, st, stage);
+      marked = st.mode == 0 && p.tn.mode == B2BFS_MODE_DIRECTION_OPT && st.bu_levels == 0 && st.level >= 1;
+      if (st.mode == 0) phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x, nullptr, marked);
+      else phase_bottom_up(p, st, stage);
       grid.sync();
       trace_mark(p.s.ctl, ntrace, st.level, ph);
       const LevelSlot* ns = &p.s.ctl->slot[(st.level + 1) & 3];
@@ -906,7 +926,13 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
                    ld_volatile(&ns->bu_count), ld_volatile(&ns->edges));
     }
     if (cv == kQueueToBitmap) {
-      phase_queue_to_bitmap(p, st);
+      if (!marked) {  // a marking top-down level has already left the new frontier in bitmap[0]
+        phase_queue_to_bitmap(p, st);
+        grid.sync();
+        trace_mark(p.s.ctl, ntrace, st.level, 3);
+      }
+    } else if (marked && !st.done) {
+      phase_unmark(p, st);
       grid.sync();
       trace_mark(p.s.ctl, ntrace, st.level, 3);
     } else if (cv == kBitmapToQueue) {
