@@ -73,6 +73,10 @@ def lib() -> C.CDLL:
             "b2bfs_get_option": ([vp, C.c_char_p, C.POINTER(i64)], C.c_int),
             "b2bfs_load_edge_file": ([vp, C.c_char_p], C.c_int),
             "b2bfs_load_edges": ([vp, i64, i64, i32p, i32p], C.c_int),
+            "b2bfs_load_graph_file": ([vp, C.c_char_p, C.c_int], C.c_int),
+            "b2bfs_save_edge_cache": ([vp, C.c_char_p], C.c_int),
+            "b2bfs_read_graph_file": ([C.c_char_p, C.c_int, C.POINTER(i64), C.POINTER(i64), C.POINTER(vp), C.POINTER(vp)], C.c_int),
+            "b2bfs_free_edges": ([vp, vp], None),
             "b2bfs_generate": ([vp, C.c_int, C.c_int, C.c_int, C.c_uint64], C.c_int),
             "b2bfs_num_vertices": ([vp, C.POINTER(i64)], C.c_int),
             "b2bfs_num_edges": ([vp, C.POINTER(i64)], C.c_int),
@@ -114,6 +118,24 @@ def search_noalloc(device: int, n: int, entries: int, rowptr_ptr: int, col_ptr: 
     if rc:
         raise B2BfsError(rc, lib().b2bfs_noalloc_last_error().decode())
     return levels.value
+
+
+FORMAT_AUTO, FORMAT_REFERENCE, FORMAT_MTX, FORMAT_SNAP, FORMAT_CACHE = -1, 0, 1, 2, 3
+
+
+def read_graph_file(path: str, fmt: int = FORMAT_AUTO):
+    """Host-only parse of a graph file (no GPU): returns (n, src, dst) as numpy arrays."""
+    n, m = C.c_int64(), C.c_int64()
+    ps, pd = C.c_void_p(), C.c_void_p()
+    rc = lib().b2bfs_read_graph_file(os.fsencode(path), fmt, C.byref(n), C.byref(m), C.byref(ps), C.byref(pd))
+    if rc:
+        raise B2BfsError(rc, lib().b2bfs_last_error(None).decode())
+    try:
+        src = np.ctypeslib.as_array(C.cast(ps, C.POINTER(C.c_int32)), shape=(max(m.value, 1),))[:m.value].copy()
+        dst = np.ctypeslib.as_array(C.cast(pd, C.POINTER(C.c_int32)), shape=(max(m.value, 1),))[:m.value].copy()
+    finally:
+        lib().b2bfs_free_edges(ps, pd)
+    return n.value, src, dst
 
 
 def comm_unique_id() -> bytes:
@@ -206,6 +228,12 @@ class Bfs:
     # -- graph
     def load_edge_file(self, path: str):
         self._check(lib().b2bfs_load_edge_file(self._h, os.fsencode(path)))
+
+    def load_graph_file(self, path: str, fmt: int = FORMAT_AUTO):
+        self._check(lib().b2bfs_load_graph_file(self._h, os.fsencode(path), fmt))
+
+    def save_edge_cache(self, path: str):
+        self._check(lib().b2bfs_save_edge_cache(self._h, os.fsencode(path)))
 
     def load_edges(self, n: int, src, dst):
         src = np.ascontiguousarray(src, np.int32)

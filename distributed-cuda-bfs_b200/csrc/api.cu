@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <thread>
+#include <vector>
 
 #include "../../include/b2bfs_graphgen.h"
 #include "bfs.cuh"
@@ -260,6 +261,85 @@ static BfsParams make_params(const b2bfs* h) {
   return p;
 }
 
+// ---------------------------------------------------------------------------------------------
+// graph files of any supported format -> host tuple arrays (malloc or page-locked)
+// ---------------------------------------------------------------------------------------------
+static int alloc_tuples(bool pinned, int64_t m, int32_t** src, int32_t** dst) {
+  const size_t bytes = (size_t)(m > 0 ? m : 1) * sizeof(int32_t);
+  *src = *dst = nullptr;
+  if (pinned) {
+    if (cudaMallocHost(src, bytes) != cudaSuccess || cudaMallocHost(dst, bytes) != cudaSuccess) {
+      cudaFreeHost(*src);
+      *src = nullptr;
+      return B2BFS_ERR_NOMEM;
+    }
+  } else {
+    *src = static_cast<int32_t*>(malloc(bytes));
+    *dst = static_cast<int32_t*>(malloc(bytes));
+    if (!*src || !*dst) { free(*src); free(*dst); *src = *dst = nullptr; return B2BFS_ERR_NOMEM; }
+  }
+  return B2BFS_OK;
+}
+static void free_tuples(bool pinned, int32_t* src, int32_t* dst) {
+  if (pinned) { cudaFreeHost(src); cudaFreeHost(dst); } else { free(src); free(dst); }
+}
+
+static int read_graph_file(const char* path, int format, bool pinned, int64_t* n_out, int64_t* m_out, int32_t** src,
+                           int32_t** dst, std::string* err) {
+  MappedFile f;
+  int rc = map_file(path, &f, err);
+  if (rc) return rc;
+  if (format == kFormatAuto) format = detect_format(f);
+  unsigned hc = std::thread::hardware_concurrency();
+  const int threads = hc ? (int)hc : 4;
+  int64_t n = 0, m = 0;
+  *src = *dst = nullptr;
+  if (format == kFormatReference) {
+    size_t body = 0;
+    rc = parse_header(f, &n, &m, &body, err);
+    if (!rc && n < 1) { rc = B2BFS_ERR_FORMAT; *err = "vertex_num must be at least 1"; }
+    if (!rc) rc = alloc_tuples(pinned, m, src, dst);
+    if (!rc) rc = parse_body(f, body, n, m, *src, *dst, threads, err);
+  } else if (format == kFormatMatrixMarket || format == kFormatSnap) {
+    size_t body = 0;
+    int64_t declared = 0;
+    if (format == kFormatMatrixMarket) rc = parse_mtx_header(f, &n, &declared, &body, err);
+    LinePlan plan;
+    if (!rc) rc = plan_lines(f, body, format == kFormatSnap ? '#' : '%', format == kFormatMatrixMarket ? 1 : 0, threads, &plan, err);
+    if (!rc && format == kFormatMatrixMarket && plan.m != declared) {
+      rc = B2BFS_ERR_FORMAT;
+      *err = "MatrixMarket file declares " + std::to_string(declared) + " entries but holds " + std::to_string(plan.m);
+    }
+    m = plan.m;
+    if (!rc) rc = alloc_tuples(pinned, m, src, dst);
+    int64_t max_id = -1;
+    if (!rc) rc = fill_lines(f, plan, format == kFormatMatrixMarket ? n : 0, *src, *dst, &max_id, err);
+    if (!rc && format == kFormatSnap) n = max_id + 1;
+    if (!rc && n < 1) { rc = B2BFS_ERR_FORMAT; *err = "the file holds no edges"; }
+  } else if (format == kFormatBinaryCache) {
+    if (f.size < 24 || memcmp(f.data, "B2BFSEDG", 8) != 0) { rc = B2BFS_ERR_FORMAT; *err = "not a b2bfs edge cache"; }
+    if (!rc) {
+      memcpy(&n, f.data + 8, 8);
+      memcpy(&m, f.data + 16, 8);
+      if (n < 1 || n > 0x7fffffffLL || m < 0 || f.size < 24 + (size_t)m * 8) { rc = B2BFS_ERR_FORMAT; *err = "edge cache is truncated"; }
+    }
+    if (!rc) rc = alloc_tuples(pinned, m, src, dst);
+    if (!rc) {
+      memcpy(*src, f.data + 24, (size_t)m * 4);
+      memcpy(*dst, f.data + 24 + (size_t)m * 4, (size_t)m * 4);
+    }
+  } else {
+    rc = B2BFS_ERR_ARG;
+    *err = "unknown graph file format";
+  }
+  unmap_file(&f);
+  if (rc == B2BFS_ERR_NOMEM && err->empty()) *err = "cannot allocate host memory for the edge list";
+  if (rc) { free_tuples(pinned, *src, *dst); *src = *dst = nullptr; return rc; }
+  *n_out = n;
+  *m_out = m;
+  return B2BFS_OK;
+}
+
 extern "C" {
 
 const char* b2bfs_version(void) { return "b2bfs 0.1 (sm_100a)"; }
@@ -404,32 +484,43 @@ int b2bfs_load_edges(b2bfs_t* h, int64_t n, int64_t m, const int32_t* src, const
   return finish_load(h);
 }
 
-int b2bfs_load_edge_file(b2bfs_t* h, const char* path) {
-  if (!h || !path) return fail(h, B2BFS_ERR_ARG, "b2bfs_load_edge_file: null argument");
-  MappedFile f;
-  std::string err;
-  int rc = map_file(path, &f, &err);
-  if (rc) return fail(h, rc, err);
+int b2bfs_load_graph_file(b2bfs_t* h, const char* path, int format) {
+  if (!h || !path) return fail(h, B2BFS_ERR_ARG, "b2bfs_load_graph_file: null argument");
   int64_t n = 0, m = 0;
-  size_t body = 0;
-  rc = parse_header(f, &n, &m, &body, &err);
-  if (rc) { unmap_file(&f); return fail(h, rc, err); }
-  if (n < 1) { unmap_file(&f); return fail(h, B2BFS_ERR_FORMAT, "vertex_num must be at least 1"); }
   int32_t *src = nullptr, *dst = nullptr;
-  const size_t bytes = (size_t)(m > 0 ? m : 1) * sizeof(int32_t);
-  if (cudaMallocHost(&src, bytes) != cudaSuccess || cudaMallocHost(&dst, bytes) != cudaSuccess) {
-    cudaFreeHost(src);
-    unmap_file(&f);
-    return fail(h, B2BFS_ERR_NOMEM, "cannot allocate page-locked staging for the edge list");
-  }
-  unsigned hc = std::thread::hardware_concurrency();
-  rc = parse_body(f, body, n, m, src, dst, hc ? (int)hc : 4, &err);
-  unmap_file(&f);
-  if (rc == B2BFS_OK) rc = b2bfs_load_edges(h, n, m, src, dst);
-  else fail(h, rc, err);
-  cudaFreeHost(src);
-  cudaFreeHost(dst);
+  std::string err;
+  int rc = read_graph_file(path, format, true, &n, &m, &src, &dst, &err);
+  if (rc) return fail(h, rc, err);
+  rc = b2bfs_load_edges(h, n, m, src, dst);
+  free_tuples(true, src, dst);
   return rc;
+}
+
+int b2bfs_load_edge_file(b2bfs_t* h, const char* path) { return b2bfs_load_graph_file(h, path, kFormatReference); }
+
+int b2bfs_read_graph_file(const char* path, int format, int64_t* n, int64_t* m, int32_t** src, int32_t** dst) {
+  if (!path || !n || !m || !src || !dst) return fail(nullptr, B2BFS_ERR_ARG, "b2bfs_read_graph_file: null argument");
+  std::string err;
+  const int rc = read_graph_file(path, format, false, n, m, src, dst, &err);
+  return rc ? fail(nullptr, rc, err) : B2BFS_OK;
+}
+
+void b2bfs_free_edges(int32_t* src, int32_t* dst) { free_tuples(false, src, dst); }
+
+int b2bfs_save_edge_cache(b2bfs_t* h, const char* path) {
+  if (!h || !path) return fail(h, B2BFS_ERR_ARG, "b2bfs_save_edge_cache: null argument");
+  if (!h->has_graph || !h->d_src) return fail(h, B2BFS_ERR_STATE, "input tuples are not resident (keep_edges=0?)");
+  API_CUDA(h, cudaSetDevice(h->device));
+  FILE* f = fopen(path, "wb");
+  if (!f) return fail(h, B2BFS_ERR_IO, std::string("cannot write ") + path);
+  std::vector<int32_t> buf((size_t)(h->m > 0 ? h->m : 1));
+  bool ok = fwrite("B2BFSEDG", 1, 8, f) == 8 && fwrite(&h->n, 8, 1, f) == 1 && fwrite(&h->m, 8, 1, f) == 1;
+  for (int pass = 0; pass < 2 && ok; ++pass) {
+    if (cudaMemcpy(buf.data(), pass ? h->d_dst : h->d_src, (size_t)h->m * 4, cudaMemcpyDeviceToHost) != cudaSuccess) ok = false;
+    else ok = h->m == 0 || fwrite(buf.data(), 4, (size_t)h->m, f) == (size_t)h->m;
+  }
+  ok = (fclose(f) == 0) && ok;
+  return ok ? B2BFS_OK : fail(h, B2BFS_ERR_IO, std::string("short write to ") + path);
 }
 
 int b2bfs_generate(b2bfs_t* h, int kind, int scale, int edgefactor, uint64_t seed) {

@@ -15,6 +15,8 @@
 //   --engine fused|stepwise
 //   --no-dedup            keep duplicate entries and self-loops in the CSR, as the reference does
 //   --gen KIND:SCALE:EF:SEED   ignore <edge_file>, generate rmat|kron|grid in HBM instead
+//   --format auto|ref|mtx|snap|bin   how to read <edge_file> (default ref, the reference's format)
+//   --save-cache PATH     also write the tuples as a binary cache for the next run
 //   --device N
 #include <chrono>
 #include <climits>
@@ -67,6 +69,8 @@ int main(int argc, char** argv) {
   bool check = true, dedup = true;
   const char* dump = nullptr;
   const char* gen = nullptr;
+  const char* save_cache = nullptr;
+  int format = B2BFS_FORMAT_REFERENCE;
   int mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED, device = 0;
   for (int i = 3; i < argc; ++i) {
     const std::string a(argv[i]);
@@ -75,6 +79,12 @@ int main(int argc, char** argv) {
     else if (a == "--dump-depth" && i + 1 < argc) dump = argv[++i];
     else if (a == "--gen" && i + 1 < argc) gen = argv[++i];
     else if (a == "--device" && i + 1 < argc) device = atoi(argv[++i]);
+    else if (a == "--save-cache" && i + 1 < argc) save_cache = argv[++i];
+    else if (a == "--format" && i + 1 < argc) {
+      const std::string f(argv[++i]);
+      format = f == "auto" ? B2BFS_FORMAT_AUTO : f == "mtx" ? B2BFS_FORMAT_MTX : f == "snap" ? B2BFS_FORMAT_SNAP
+             : f == "bin" ? B2BFS_FORMAT_CACHE : B2BFS_FORMAT_REFERENCE;
+    }
     else if (a == "--mode" && i + 1 < argc) mode = strcmp(argv[++i], "td") == 0 ? B2BFS_MODE_TOP_DOWN : B2BFS_MODE_DIRECTION_OPT;
     else if (a == "--engine" && i + 1 < argc) engine = strcmp(argv[++i], "stepwise") == 0 ? B2BFS_ENGINE_STEPWISE : B2BFS_ENGINE_FUSED;
     else { fprintf(stderr, "b2bfs: unknown argument %s\n", argv[i]); return 2; }
@@ -97,11 +107,15 @@ int main(int argc, char** argv) {
     rc = b2bfs_generate(h, k, scale, ef, seed);
     if (rc) return die(h, "b2bfs_generate", rc);
   } else {
-    rc = b2bfs_load_edge_file(h, path);
+    rc = b2bfs_load_graph_file(h, path, format);
     if (rc) {
       if (rc == B2BFS_ERR_IO) printf("not open %s\n", path);  // bfs.cu:878
-      return die(h, "b2bfs_load_edge_file", rc);
+      return die(h, "b2bfs_load_graph_file", rc);
     }
+  }
+  if (save_cache) {
+    rc = b2bfs_save_edge_cache(h, save_cache);
+    if (rc) return die(h, "b2bfs_save_edge_cache", rc);
   }
   int64_t n = 0, m = 0, e2 = 0;
   b2bfs_num_vertices(h, &n);

@@ -170,3 +170,145 @@ int parse_body(const MappedFile& f, size_t body_off, int64_t n, int64_t m, int32
 }
 
 }  // namespace b2
+
+// ---------------------------------------------------------------------------------------------
+// line-oriented formats (MatrixMarket coordinate files, SNAP edge lists)
+// ---------------------------------------------------------------------------------------------
+namespace b2 {
+
+int detect_format(const MappedFile& f) {
+  const char* p = f.data;
+  const char* end = f.data + f.size;
+  if (f.size >= 8 && memcmp(p, "B2BFSEDG", 8) == 0) return kFormatBinaryCache;
+  if (f.size >= 14 && memcmp(p, "%%MatrixMarket", 14) == 0) return kFormatMatrixMarket;
+  while (p < end && is_space(*p)) ++p;
+  if (p < end && *p == '#') return kFormatSnap;
+  if (p < end && *p == '%') return kFormatMatrixMarket;
+  return kFormatReference;
+}
+
+static inline const char* line_end(const char* p, const char* end) {
+  while (p < end && *p != '\n') ++p;
+  return p;
+}
+
+// a data line = first non-blank character is neither the comment character nor a line break
+static inline bool is_data_line(const char* p, const char* le, char comment) {
+  while (p < le && (*p == ' ' || *p == '\t' || *p == '\r')) ++p;
+  return p < le && *p != comment && *p != '%';
+}
+
+int parse_mtx_header(const MappedFile& f, int64_t* n, int64_t* nnz, size_t* body_off, std::string* err) {
+  const char* p = f.data;
+  const char* end = f.data + f.size;
+  while (p < end) {
+    const char* le = line_end(p, end);
+    if (is_data_line(p, le, '%')) {
+      int64_t v[3];
+      const char* q = p;
+      for (int k = 0; k < 3; ++k) {
+        while (q < le && is_space(*q)) ++q;
+        if (!parse_uint(q, le, &v[k])) {
+          *err = "MatrixMarket size line must be: rows cols nonzeros";
+          return B2BFS_ERR_FORMAT;
+        }
+      }
+      *n = v[0] > v[1] ? v[0] : v[1];
+      *nnz = v[2];
+      if (*n > 0x7fffffffLL) { *err = "matrix dimension exceeds int32 ids"; return B2BFS_ERR_RANGE; }
+      *body_off = (size_t)((le < end ? le + 1 : le) - f.data);
+      return B2BFS_OK;
+    }
+    p = le < end ? le + 1 : le;
+  }
+  *err = "MatrixMarket file has no size line";
+  return B2BFS_ERR_FORMAT;
+}
+
+int plan_lines(const MappedFile& f, size_t body_off, char comment, int64_t id_base, int threads, LinePlan* plan,
+               std::string* err) {
+  (void)err;
+  const char* base = f.data;
+  const size_t size = f.size;
+  if (threads < 1) threads = 1;
+  const size_t span = size > body_off ? size - body_off : 0;
+  if (span / 4096 < (size_t)threads) threads = (int)(span / 4096) + 1;
+  plan->comment = comment;
+  plan->id_base = id_base;
+  plan->cut.assign(threads + 1, size);
+  for (int t = 0; t < threads; ++t) {
+    size_t b = body_off + span * (size_t)t / (size_t)threads;
+    if (t > 0) while (b < size && base[b - 1] != '\n') ++b;  // ranges start at line starts
+    plan->cut[t] = b;
+  }
+  std::vector<int64_t> cnt(threads, 0);
+  auto count = [&](int t) {
+    const char* p = base + plan->cut[t];
+    const char* e = base + plan->cut[t + 1];
+    int64_t c = 0;
+    while (p < e) {
+      const char* le = line_end(p, base + size);
+      c += is_data_line(p, le, comment);
+      p = le + 1;
+    }
+    cnt[t] = c;
+  };
+  {
+    std::vector<std::thread> th;
+    for (int t = 1; t < threads; ++t) th.emplace_back(count, t);
+    count(0);
+    for (auto& x : th) x.join();
+  }
+  plan->first.assign(threads + 1, 0);
+  for (int t = 0; t < threads; ++t) plan->first[t + 1] = plan->first[t] + cnt[t];
+  plan->m = plan->first[threads];
+  return B2BFS_OK;
+}
+
+int fill_lines(const MappedFile& f, const LinePlan& plan, int64_t n_limit, int32_t* src, int32_t* dst, int64_t* max_id,
+               std::string* err) {
+  const char* base = f.data;
+  const size_t size = f.size;
+  const int threads = (int)plan.cut.size() - 1;
+  std::atomic<int> status(B2BFS_OK);
+  std::vector<int64_t> mx(threads, -1);
+  auto fill = [&](int t) {
+    const char* p = base + plan.cut[t];
+    const char* e = base + plan.cut[t + 1];
+    int64_t k = plan.first[t], local_max = -1;
+    while (p < e) {
+      const char* le = line_end(p, base + size);
+      if (is_data_line(p, le, plan.comment)) {
+        int64_t v[2];
+        const char* q = p;
+        for (int j = 0; j < 2; ++j) {
+          while (q < le && is_space(*q)) ++q;
+          if (!parse_uint(q, le, &v[j])) { status.store(B2BFS_ERR_FORMAT); return; }
+          v[j] -= plan.id_base;
+          if (v[j] < 0 || v[j] > 0x7ffffffeLL || (n_limit > 0 && v[j] >= n_limit)) { status.store(B2BFS_ERR_RANGE); return; }
+          if (v[j] > local_max) local_max = v[j];
+        }
+        src[k] = (int32_t)v[0];
+        dst[k] = (int32_t)v[1];
+        ++k;
+      }
+      p = le + 1;
+    }
+    mx[t] = local_max;
+  };
+  {
+    std::vector<std::thread> th;
+    for (int t = 1; t < threads; ++t) th.emplace_back(fill, t);
+    fill(0);
+    for (auto& x : th) x.join();
+  }
+  int64_t m = -1;
+  for (int t = 0; t < threads; ++t) if (mx[t] > m) m = mx[t];
+  if (max_id) *max_id = m;
+  const int rc = status.load();
+  if (rc == B2BFS_ERR_FORMAT) *err = "a data line does not start with two non-negative integers";
+  if (rc == B2BFS_ERR_RANGE) *err = "a vertex id is outside the declared range";
+  return rc;
+}
+
+}  // namespace b2

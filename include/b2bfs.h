@@ -96,6 +96,30 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value);
  * Unlike the reference, short files, ids >= vertex_num and unreadable paths are errors. */
 int b2bfs_load_edge_file(b2bfs_t* h, const char* path);
 
+/* Wider ingest.  The only dataset the reference's README names,
+ * soc-LiveJournal1.mtx (README.md:22), cannot be read by the reference's own loader ('%' comments,
+ * a 3-number header and 1-based ids, vs bfs.cu:845-861).  `format`:
+ *   B2BFS_FORMAT_AUTO (-1)      sniff: cache magic, "%%MatrixMarket"/'%', leading '#', else reference
+ *   B2BFS_FORMAT_REFERENCE (0)  "vertex_num edge_num" + "src dst" pairs, 0-based
+ *   B2BFS_FORMAT_MTX (1)        MatrixMarket coordinate: '%' comments, "rows cols nnz", 1-based
+ *                               "i j [value]" lines (values ignored); n = max(rows, cols)
+ *   B2BFS_FORMAT_SNAP (2)       '#' comment lines, one 0-based "u v" per line; n = max id + 1
+ *   B2BFS_FORMAT_CACHE (3)      binary edge cache written by b2bfs_save_edge_cache
+ * All text formats are parsed by every host thread over a memory-mapped file. */
+#define B2BFS_FORMAT_AUTO (-1)
+#define B2BFS_FORMAT_REFERENCE 0
+#define B2BFS_FORMAT_MTX 1
+#define B2BFS_FORMAT_SNAP 2
+#define B2BFS_FORMAT_CACHE 3
+int b2bfs_load_graph_file(b2bfs_t* h, const char* path, int format);
+/* Write the resident input tuples as a binary cache ("B2BFSEDG", n, m as int64, src[m], dst[m] as
+ * int32) so that a multi-gigabyte text file is parsed once. */
+int b2bfs_save_edge_cache(b2bfs_t* h, const char* path);
+/* Host-only: parse a graph file into malloc'ed tuple arrays (no GPU involved; release them with
+ * b2bfs_free_edges).  What b2bfs_load_graph_file feeds to b2bfs_load_edges. */
+int b2bfs_read_graph_file(const char* path, int format, int64_t* n, int64_t* m, int32_t** src, int32_t** dst);
+void b2bfs_free_edges(int32_t* src, int32_t* dst);
+
 /* Load a graph from host arrays of m (src,dst) tuples over n vertices (0-based ids).
  * Replaces filling `struct Graph` (bfs.cu:21-27, 851-875) + initCuda2's cudaMalloc/cudaMemcpy. */
 int b2bfs_load_edges(b2bfs_t* h, int64_t n, int64_t m, const int32_t* src, const int32_t* dst);
