@@ -6,7 +6,7 @@ sys.path.insert(0, ROOT)
 import numpy as np
 import oracle
 b2 = importlib.import_module("distributed-cuda-bfs_b200")
-REF = os.path.join(ROOT, "oracle", "_ref", "ref_gpu_bfs")
+REF = os.path.join(ROOT, "oracle", "_ref", "ref_gpu_bfs_2dev" if os.environ.get("REF_2DEV") else "ref_gpu_bfs")
 ASIS = os.path.join(ROOT, "oracle", "_ref", "ref_gpu_bfs_asshipped")
 scales = [int(x) for x in sys.argv[1:]] or [16, 18]
 tmp = tempfile.mkdtemp()
