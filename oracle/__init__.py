@@ -68,6 +68,9 @@ def lib() -> C.CDLL:
         L.oracle_validate_tree.restype = C.c_int
         L.oracle_reach_stats.argtypes = [C.c_int64, _i32p, _i32p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.oracle_reach_stats.restype = None
+        L.oracle_bfs_parallel.argtypes = [C.c_int64, _i64p, _i32p, _i32p, C.c_int64, _i32p, C.c_int]
+        L.oracle_bfs_parallel.restype = C.c_int64
+        L.oracle_num_threads.restype = C.c_int
         _lib = L
     return _lib
 
@@ -152,6 +155,20 @@ def bfs_serial(g: Csr, start: int, want_parent: bool = False):
     if rc < 0:
         raise ValueError(f"oracle_bfs_serial -> {rc}")
     return (depth, parent) if want_parent else depth
+
+
+def bfs_parallel(g: Csr, start: int, threads: int = 0):
+    """Multi-core level-synchronous port; same depths as bfs_serial.
+    threads = 0: all online cores."""
+    depth = np.empty(g.n, np.int32)
+    rc = lib().oracle_bfs_parallel(g.n, g.offsets, g.sizes, g.adj, start, depth, threads)
+    if rc < 0:
+        raise ValueError(f"oracle_bfs_parallel -> {rc}")
+    return depth
+
+
+def num_threads() -> int:
+    return int(lib().oracle_num_threads())
 
 
 def bfs_kdev(g: Csr, start: int, k: int):

@@ -302,3 +302,116 @@ void oracle_reach_stats(int64_t n, const int32_t* sizes, const int32_t* depth, i
   *v_r = vr;
   *d_r = dr;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * Multi-core host BFS: a level-synchronous PORT of bfsCPU (bfs.cu:923-945) for all
+ * host cores — same CSR, same depths; one frontier array per level, claims by compare-and-swap on
+ * the depth array, per-thread chunks appended to the next frontier.  Not the reference's code
+ * (which is serial); it exists so that the CPU baseline is not flattered by using one core.
+ * POSIX threads + a barrier per level.  Returns the number of vertices reached.
+ * ------------------------------------------------------------------------------------------- */
+#include <pthread.h>
+#include <unistd.h>
+
+int oracle_num_threads(void) {
+  long c = sysconf(_SC_NPROCESSORS_ONLN);
+  return c < 1 ? 1 : (c > 64 ? 64 : (int)c);
+}
+
+typedef struct {
+  int64_t n;
+  const int64_t* offsets;
+  const int32_t* sizes;
+  const int32_t* adj;
+  int32_t* depth;
+  int32_t *cur, *nxt;
+  int64_t ncur, nnext, cursor, reached;
+  int32_t level;
+  int threads, done;
+  pthread_barrier_t bar;
+} par_bfs_t;
+
+typedef struct { par_bfs_t* s; int tid; } par_arg_t;
+
+static void* par_bfs_worker(void* argp) {
+  par_arg_t* a = (par_arg_t*)argp;
+  par_bfs_t* s = a->s;
+  enum { CHUNK = 1024, GRAB = 64 };
+  int32_t local[CHUNK];
+  for (int64_t v = (int64_t)a->tid; v < s->n; v += s->threads) s->depth[v] = INT_MAX;
+  pthread_barrier_wait(&s->bar);
+  for (;;) {
+    pthread_barrier_wait(&s->bar); /* thread 0 has published the level */
+    if (s->done) break;
+    int cnt = 0;
+    for (;;) {
+      const int64_t t0 = __atomic_fetch_add(&s->cursor, (int64_t)GRAB, __ATOMIC_RELAXED);
+      if (t0 >= s->ncur) break;
+      const int64_t t1 = t0 + GRAB < s->ncur ? t0 + GRAB : s->ncur;
+      for (int64_t t = t0; t < t1; ++t) {
+        const int32_t u = s->cur[t];
+        const int64_t b = s->offsets[u], e = b + s->sizes[u];
+        for (int64_t i = b; i < e; ++i) {
+          const int32_t v = s->adj[i];
+          int32_t expect = INT_MAX;
+          if (__atomic_load_n(&s->depth[v], __ATOMIC_RELAXED) == INT_MAX &&
+              __atomic_compare_exchange_n(&s->depth[v], &expect, s->level + 1, 0, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) {
+            local[cnt++] = v;
+            if (cnt == CHUNK) {
+              const int64_t at = __atomic_fetch_add(&s->nnext, (int64_t)cnt, __ATOMIC_RELAXED);
+              memcpy(s->nxt + at, local, (size_t)cnt * sizeof(int32_t));
+              cnt = 0;
+            }
+          }
+        }
+      }
+    }
+    if (cnt) {
+      const int64_t at = __atomic_fetch_add(&s->nnext, (int64_t)cnt, __ATOMIC_RELAXED);
+      memcpy(s->nxt + at, local, (size_t)cnt * sizeof(int32_t));
+    }
+    pthread_barrier_wait(&s->bar); /* level complete */
+    if (a->tid == 0) {
+      int32_t* tmp = s->cur; s->cur = s->nxt; s->nxt = tmp;
+      s->ncur = s->nnext;
+      s->reached += s->nnext;
+      s->nnext = 0;
+      s->cursor = 0;
+      s->level++;
+      s->done = s->ncur == 0;
+    }
+  }
+  return NULL;
+}
+
+int64_t oracle_bfs_parallel(int64_t n, const int64_t* offsets, const int32_t* sizes, const int32_t* adj,
+                            int64_t start, int32_t* depth, int threads) {
+  if (start < 0 || start >= n) return ORACLE_ERR_RANGE;
+  if (threads < 1) threads = oracle_num_threads();
+  par_bfs_t s;
+  memset(&s, 0, sizeof(s));
+  s.n = n; s.offsets = offsets; s.sizes = sizes; s.adj = adj; s.depth = depth; s.threads = threads;
+  s.cur = (int32_t*)malloc((size_t)n * sizeof(int32_t));
+  s.nxt = (int32_t*)malloc((size_t)n * sizeof(int32_t));
+  if (!s.cur || !s.nxt) { free(s.cur); free(s.nxt); return ORACLE_ERR_NOMEM; }
+  pthread_barrier_init(&s.bar, NULL, (unsigned)threads + 1);
+  pthread_t* th = (pthread_t*)malloc((size_t)threads * sizeof(pthread_t));
+  par_arg_t* args = (par_arg_t*)malloc((size_t)threads * sizeof(par_arg_t));
+  for (int t = 0; t < threads; ++t) { args[t].s = &s; args[t].tid = t; pthread_create(&th[t], NULL, par_bfs_worker, &args[t]); }
+  pthread_barrier_wait(&s.bar); /* depth array filled */
+  depth[start] = 0;
+  s.cur[0] = (int32_t)start;
+  s.ncur = 1; s.reached = 1;
+  /* the coordinator only takes part in the barriers; workers run the levels */
+  for (;;) {
+    pthread_barrier_wait(&s.bar);
+    if (s.done) break;
+    pthread_barrier_wait(&s.bar);
+    /* thread 0 of the workers advances the level right after this barrier; wait for it at the next one */
+  }
+  for (int t = 0; t < threads; ++t) pthread_join(th[t], NULL);
+  pthread_barrier_destroy(&s.bar);
+  const int64_t reached = s.reached;
+  free(th); free(args); free(s.cur); free(s.nxt);
+  return reached;
+}

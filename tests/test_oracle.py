@@ -188,3 +188,14 @@ def test_algorithmic_bytes_formula():
     # reached {0,1,2,3}: D_r = 2+3+2+3 = 10, V_r = 4  ->  4*10 + 8*4 + 8*6
     assert oracle.reach_stats(g, depth) == (4, 10)
     assert oracle.algorithmic_bytes(g, depth) == 40 + 32 + 48
+
+
+@pytest.mark.parametrize("kind,scale", [(oracle.GEN_RMAT, 13), (oracle.GEN_KRON, 12), (oracle.GEN_GRID, 10)])
+def test_multicore_port_equals_serial(kind, scale):
+    """the all-cores port of bfsCPU gives the serial depths for any thread count."""
+    n, s, d = oracle.generate_edges(kind, scale, 16, 2)
+    g = oracle.build_csr(n, s, d)
+    for root in (0, 2, n - 1):
+        want = oracle.bfs_serial(g, root)
+        for threads in (1, 3, 0):
+            assert oracle.check_output(oracle.bfs_parallel(g, root, threads), want) == -1
