@@ -321,12 +321,21 @@ static int read_graph_file(const char* path, int format, bool pinned, int64_t* n
     if (!rc) {
       memcpy(&n, f.data + 8, 8);
       memcpy(&m, f.data + 16, 8);
-      if (n < 1 || n > 0x7fffffffLL || m < 0 || f.size < 24 + (size_t)m * 8) { rc = B2BFS_ERR_FORMAT; *err = "edge cache is truncated"; }
+      // m is bounded by what the file can hold BEFORE any multiplication (a crafted m >= 2^61 would wrap)
+      if (n < 1 || n > 0x7fffffffLL || m < 0 || (uint64_t)m > (uint64_t)(f.size - 24) / 8) { rc = B2BFS_ERR_FORMAT; *err = "edge cache is truncated"; }
     }
     if (!rc) rc = alloc_tuples(pinned, m, src, dst);
     if (!rc) {
       memcpy(*src, f.data + 24, (size_t)m * 4);
       memcpy(*dst, f.data + 24 + (size_t)m * 4, (size_t)m * 4);
+      for (int64_t i = 0; i < m; ++i) {  // the text parsers range-check while they parse; do the same here
+        if ((uint32_t)(*src)[i] >= (uint32_t)n || (uint32_t)(*dst)[i] >= (uint32_t)n) {
+          rc = B2BFS_ERR_RANGE;
+          *err = "edge cache holds vertex id " + std::to_string((uint32_t)(*src)[i] >= (uint32_t)n ? (*src)[i] : (*dst)[i]) +
+                 " >= vertex_num " + std::to_string(n);
+          break;
+        }
+      }
     }
   } else {
     rc = B2BFS_ERR_ARG;
@@ -356,16 +365,26 @@ int b2bfs_create(b2bfs_t** out, int device) {
   if (device < 0 || device >= count) return fail(nullptr, B2BFS_ERR_ARG, "b2bfs_create: device index out of range");
   b2bfs* h = new b2bfs();
   h->device = device;
-  API_CUDA(nullptr, cudaSetDevice(device));
-  int coop = 0;
-  API_CUDA(nullptr, cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
-  if (!coop) { delete h; return fail(nullptr, B2BFS_ERR_UNSUPPORTED, "device lacks cooperative launch"); }
-  API_CUDA(nullptr, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-  API_CUDA(nullptr, cudaEventCreate(&h->ev0));
-  API_CUDA(nullptr, cudaEventCreate(&h->ev1));
-  API_CUDA(nullptr, cudaMallocHost(&h->pinned_ctl, sizeof(Control)));
-  Status s = search_grid_size(device, &h->grid);
-  if (!s.ok()) { delete h; return fail(nullptr, s); }
+  // any failure from here on releases what was created so far (b2bfs_destroy copes with a half-built handle)
+  auto create = [&]() -> int {
+    API_CUDA(nullptr, cudaSetDevice(device));
+    int coop = 0;
+    API_CUDA(nullptr, cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
+    if (!coop) return fail(nullptr, B2BFS_ERR_UNSUPPORTED, "device lacks cooperative launch");
+    API_CUDA(nullptr, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    API_CUDA(nullptr, cudaEventCreate(&h->ev0));
+    API_CUDA(nullptr, cudaEventCreate(&h->ev1));
+    API_CUDA(nullptr, cudaMallocHost(&h->pinned_ctl, sizeof(Control)));
+    Status s = search_grid_size(device, &h->grid);
+    return s.ok() ? B2BFS_OK : fail(nullptr, s);
+  };
+  const int rc = create();
+  if (rc) {
+    const std::string msg = g_create_error;  // b2bfs_destroy must not disturb the message
+    b2bfs_destroy(h);
+    g_create_error = msg;
+    return rc;
+  }
   *out = h;
   return B2BFS_OK;
 }
@@ -708,7 +727,7 @@ int b2bfs_device_parent(const b2bfs_t* h, const int32_t** parent_dev) {
 }
 
 int b2bfs_last_trace(b2bfs_t* h, int32_t* level_out, int32_t* phase_out, double* us_out, int cap) {
-  if (!h || !h->has_graph || cap < 0) return B2BFS_ERR_ARG;
+  if (!h || !h->has_graph || cap < 0 || (cap > 0 && (!level_out || !phase_out || !us_out))) return B2BFS_ERR_ARG;
   if (cudaSetDevice(h->device) != cudaSuccess) return B2BFS_ERR_CUDA;
   if (cudaMemcpy(h->pinned_ctl, h->sv.ctl, sizeof(Control), cudaMemcpyDeviceToHost) != cudaSuccess) return B2BFS_ERR_CUDA;
   const Control* c = h->pinned_ctl;

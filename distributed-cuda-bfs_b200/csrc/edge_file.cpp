@@ -96,6 +96,12 @@ int parse_header(const MappedFile& f, int64_t* n, int64_t* m, size_t* body_off, 
   *n = v[0];
   *m = v[1];
   *body_off = (size_t)(p - f.data);
+  // every pair needs at least "d d " = 4 bytes: a header that promises more pairs than the rest of
+  // the file can hold is a malformed file, not a reason to attempt a huge allocation
+  if ((uint64_t)v[1] > (uint64_t)(f.size - *body_off) / 4 + 1) {
+    *err = "edge list header declares " + std::to_string(v[1]) + " edges but the file is too short to hold them";
+    return B2BFS_ERR_FORMAT;
+  }
   return B2BFS_OK;
 }
 

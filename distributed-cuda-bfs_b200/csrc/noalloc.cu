@@ -11,6 +11,12 @@
 //
 // The price is a fixed ceiling (B2BFS_NOALLOC_MAX_VERTICES / _MAX_ENTRIES) and kNoallocBytes of
 // device memory that every GPU holding this library keeps until the process exits, used or not.
+//
+// One thing the caller has to plan for: CUDA loads a library's device code lazily.  The FIRST call
+// on a device is therefore the moment the driver places this file's kernels and the scratch array
+// itself in device memory - a start-up step that takes memory once, exactly like loading any other
+// CUDA library does.  Make that first call while the process is still setting up (a one-vertex graph
+// is enough); every later call finds everything in place and takes nothing.
 #include <mutex>
 
 #include "bfs.cuh"
@@ -121,8 +127,10 @@ int b2bfs_search_noalloc(int device, int64_t n, int64_t entries, const int64_t* 
 
   cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
   unsigned char* base = ds.scratch;
-  BfsParams p;
+  BfsParams p{};
   p.g.n = n;
+  p.g.n_global = n;
+  p.g.entries_global = (unsigned long long)entries;
   p.g.nwords = ((n + 31) / 32 + 3) / 4 * 4;
   p.g.entries = entries;
   p.g.vbase = 0;

@@ -175,16 +175,25 @@ int b2bfs_last_trace(b2bfs_t* h, int32_t* level_out, int32_t* phase_out, double*
  * different allocator already owns the whole card.  The caller passes the graph as a CSR that is
  * ALREADY in device memory (rowptr: n+1 int64; col: `entries` int32, 16-byte aligned, neighbour
  * ids in [0,n)) and device buffers for the results (depth, parent: n int32 each, 16-byte aligned);
- * all scratch — bitmaps, frontier work lists, counters — lives in one array compiled into the
- * library (about 7.4 MiB per GPU, resident from load to exit).  Limits: n <= B2BFS_NOALLOC_MAX_VERTICES
+ * all scratch - bitmaps, frontier work lists, counters - lives in one array compiled into the
+ * library (about 7.4 MiB per GPU, held until the process exits).  Limits: n <= B2BFS_NOALLOC_MAX_VERTICES
  * and entries <= B2BFS_NOALLOC_MAX_ENTRIES, otherwise B2BFS_ERR_RANGE.  Top-down only; results are
- * the same as b2bfs_run's (depth INT_MAX / parent -1 = unreachable).  Blocks until the search is
- * complete on `cuda_stream` (a cudaStream_t, or NULL for the default stream).
- * The first call on a device resolves the array's device address (cudaGetSymbolAddress) and sizes
- * the launch; make that call before starting any stream capture.  All calls of a process share the
- * one array (it still holds the previous call's contents; the entry point clears what has to start
- * at zero), so two searches overlapping on the GPU would corrupt each other: the library takes a
- * host lock and returns only when the search is complete, which keeps its own calls apart. */
+ * the same as b2bfs_run's (depth INT_MAX / parent -1 = unreachable).
+ * `col` is read in 16-byte groups: when `entries` is not a multiple of 4 the last group reaches up
+ * to 12 bytes past col[entries-1].  Those bytes are read and ignored, and they lie in the same
+ * 16-byte unit as the last entry, but a caller that carves `col` out of a pool should size the
+ * piece to a multiple of 4 entries so that a memory checker stays quiet.
+ * The call blocks until the search is complete on `cuda_stream` (a cudaStream_t, or NULL for the
+ * default stream); it synchronises that stream before it returns.
+ * The first call on a device is a set-up call: it resolves the array's device address
+ * (cudaGetSymbolAddress), sizes the launch, and - because CUDA loads device code lazily - is also
+ * when the driver puts this library's kernels and the array itself on the device.  Make it during
+ * start-up, with any small graph, and before starting any stream capture; later calls on that
+ * device take no device memory at all.
+ * All calls of a process share the one array (it still holds the previous call's contents; the
+ * entry point clears what has to start at zero), so two searches overlapping on the GPU would
+ * corrupt each other: the library takes a host lock and returns only when the search is complete,
+ * which keeps its own calls apart. */
 #define B2BFS_NOALLOC_MAX_VERTICES 262144   /* 2^18 */
 #define B2BFS_NOALLOC_MAX_ENTRIES 8388608   /* 2^23 directed CSR entries */
 int b2bfs_search_noalloc(int device, int64_t n, int64_t entries, const int64_t* rowptr_dev, const int32_t* col_dev,

@@ -71,6 +71,13 @@ def lib() -> C.CDLL:
         L.oracle_bfs_parallel.argtypes = [C.c_int64, _i64p, _i32p, _i32p, C.c_int64, _i32p, C.c_int]
         L.oracle_bfs_parallel.restype = C.c_int64
         L.oracle_num_threads.restype = C.c_int
+        L.oracle_build_csr_parallel.argtypes = [C.c_int64, C.c_int64, _i32p, _i32p, _i64p, _i32p, _i32p, C.c_int]
+        L.oracle_build_csr_parallel.restype = C.c_int
+        L.oracle_check_depth_by_edges.argtypes = [C.c_int64, C.c_int64, _i32p, _i32p, C.c_int64, _i32p, C.c_int]
+        L.oracle_check_depth_by_edges.restype = C.c_int64
+        L.oracle_bfs_serial_bounded.argtypes = [C.c_int64, _i64p, _i32p, _i32p, C.c_int64, _i32p, C.c_int64,
+                                                C.POINTER(C.c_int64)]
+        L.oracle_bfs_serial_bounded.restype = C.c_int64
         _lib = L
     return _lib
 
@@ -145,6 +152,42 @@ def build_csr(n: int, src, dst) -> Csr:
     if rc:
         raise ValueError(f"oracle_build_csr -> {rc}")
     return Csr(n, offsets, sizes, adj)
+
+
+def build_csr_parallel(n: int, src, dst, threads: int = 0) -> Csr:
+    """All-cores build: same rows as build_csr as multisets, order inside a row unspecified (depths
+    do not depend on it).  For bench.py on graphs where the serial builder would take minutes."""
+    src = np.ascontiguousarray(src, np.int32)
+    dst = np.ascontiguousarray(dst, np.int32)
+    m = src.shape[0]
+    offsets = np.empty(max(n, 1), np.int64)[:n]
+    sizes = np.empty(max(n, 1), np.int32)[:n]
+    adj = np.empty(2 * m, np.int32)
+    rc = lib().oracle_build_csr_parallel(n, m, src, dst, offsets, sizes, adj, threads)
+    if rc:
+        raise ValueError(f"oracle_build_csr_parallel -> {rc}")
+    return Csr(n, offsets, sizes, adj)
+
+
+def check_depth_by_edges(n: int, src, dst, root: int, depth, threads: int = 0) -> int:
+    """-1 if `depth` is exactly the BFS depth array of `root` over the tuples (three edge rules, see
+    bfs_oracle.c), else an offending vertex.  Needs no CSR: usable at any scale the tuples fit."""
+    rc = int(lib().oracle_check_depth_by_edges(n, src.shape[0], np.ascontiguousarray(src, np.int32),
+                                               np.ascontiguousarray(dst, np.int32), root,
+                                               np.ascontiguousarray(depth, np.int32), threads))
+    if rc < -1:
+        raise ValueError(f"oracle_check_depth_by_edges -> {rc}")
+    return rc
+
+
+def bfs_serial_bounded(g: Csr, start: int, max_entries: int):
+    """(depth, entries_scanned, vertices_reached) of a serial search stopped after max_entries."""
+    depth = np.empty(g.n, np.int32)
+    reached = C.c_int64()
+    rc = lib().oracle_bfs_serial_bounded(g.n, g.offsets, g.sizes, g.adj, start, depth, max_entries, C.byref(reached))
+    if rc < 0:
+        raise ValueError(f"oracle_bfs_serial_bounded -> {rc}")
+    return depth, int(rc), reached.value
 
 
 def bfs_serial(g: Csr, start: int, want_parent: bool = False):

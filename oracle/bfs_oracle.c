@@ -415,3 +415,160 @@ int64_t oracle_bfs_parallel(int64_t n, const int64_t* offsets, const int32_t* si
   free(th); free(args); free(s.cur); free(s.nxt);
   return reached;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * Helpers for bench.py's parity / baseline legs on graphs too large for the serial builders above.
+ * None of them restates new reference arithmetic; each is checked in tests/test_oracle.py against
+ * oracle_build_csr / oracle_bfs_serial.
+ * ------------------------------------------------------------------------------------------- */
+
+/* generic "run fn(tid) on T threads" */
+typedef struct { void (*fn)(void*, int, int); void* ctx; int tid, threads; } par_job_t;
+static void* par_job_entry(void* p) {
+  par_job_t* j = (par_job_t*)p;
+  j->fn(j->ctx, j->tid, j->threads);
+  return NULL;
+}
+static void run_on_threads(void (*fn)(void*, int, int), void* ctx, int threads) {
+  if (threads < 1) threads = oracle_num_threads();
+  pthread_t* th = (pthread_t*)malloc((size_t)threads * sizeof(pthread_t));
+  par_job_t* jobs = (par_job_t*)malloc((size_t)threads * sizeof(par_job_t));
+  for (int t = 0; t < threads; ++t) {
+    jobs[t].fn = fn; jobs[t].ctx = ctx; jobs[t].tid = t; jobs[t].threads = threads;
+    pthread_create(&th[t], NULL, par_job_entry, &jobs[t]);
+  }
+  for (int t = 0; t < threads; ++t) pthread_join(th[t], NULL);
+  free(th);
+  free(jobs);
+}
+
+/* All-cores CSR build: the same multiset per row as oracle_build_csr (bfs.cu:851-875: v pushed onto
+ * u's list and u onto v's, duplicates and self-loops kept), but the ORDER inside a row is whatever
+ * the threads' atomic cursors produce, not file order.  Depths do not depend on that order (parent
+ * edge indices do), so this builder is used only where depths are compared: bench.py at scale >= 24. */
+typedef struct {
+  int64_t n, m;
+  const int32_t *src, *dst;
+  int64_t* offsets;
+  int32_t* sizes;
+  int32_t* adj;
+  int64_t* cur;
+  int bad;
+} pcsr_t;
+static void pcsr_count(void* c, int tid, int T) {
+  pcsr_t* s = (pcsr_t*)c;
+  const int64_t a = s->m * tid / T, b = s->m * (tid + 1) / T;
+  for (int64_t i = a; i < b; ++i) {
+    const int32_t u = s->src[i], v = s->dst[i];
+    if (u < 0 || v < 0 || u >= s->n || v >= s->n) { s->bad = 1; return; }
+    __atomic_fetch_add(&s->sizes[u], 1, __ATOMIC_RELAXED);
+    __atomic_fetch_add(&s->sizes[v], 1, __ATOMIC_RELAXED);
+  }
+}
+static void pcsr_fill(void* c, int tid, int T) {
+  pcsr_t* s = (pcsr_t*)c;
+  const int64_t a = s->m * tid / T, b = s->m * (tid + 1) / T;
+  for (int64_t i = a; i < b; ++i) {
+    const int32_t u = s->src[i], v = s->dst[i];
+    s->adj[__atomic_fetch_add(&s->cur[u], 1, __ATOMIC_RELAXED)] = v;
+    s->adj[__atomic_fetch_add(&s->cur[v], 1, __ATOMIC_RELAXED)] = u;
+  }
+}
+int oracle_build_csr_parallel(int64_t n, int64_t m, const int32_t* src, const int32_t* dst, int64_t* offsets,
+                              int32_t* sizes, int32_t* adj, int threads) {
+  pcsr_t s = {n, m, src, dst, offsets, sizes, adj, NULL, 0};
+  memset(sizes, 0, (size_t)n * sizeof(int32_t));
+  run_on_threads(pcsr_count, &s, threads);
+  if (s.bad) return ORACLE_ERR_RANGE;
+  int64_t run = 0;
+  for (int64_t v = 0; v < n; ++v) { offsets[v] = run; run += sizes[v]; }
+  s.cur = (int64_t*)malloc((size_t)(n > 0 ? n : 1) * sizeof(int64_t));
+  if (!s.cur) return ORACLE_ERR_NOMEM;
+  memcpy(s.cur, offsets, (size_t)n * sizeof(int64_t));
+  run_on_threads(pcsr_fill, &s, threads);
+  free(s.cur);
+  return ORACLE_OK;
+}
+
+/* Depth check straight from the edge tuples, no CSR needed.  A depth array equals bfsCPU's
+ * (bfs.cu:923-945) for `root` if and only if
+ *   (1) depth[root] == 0 and no other vertex has depth 0,
+ *   (2) for every tuple (u,v): both endpoints reached or both not, and |depth[u]-depth[v]| <= 1,
+ *   (3) every reached vertex other than the root has a tuple to a vertex one level up.
+ * (2) gives depth[v] <= dist(root,v) by induction along a shortest path and keeps unreached vertices
+ * out of the root's component; (3) gives a walk of depth[v] steps back to the root, so
+ * depth[v] >= dist.  Returns -1 when all three hold, else the first offending vertex found
+ * (a vertex id >= 0).  All host cores; two streaming passes over the tuples. */
+typedef struct {
+  int64_t n, m, root;
+  const int32_t *src, *dst, *depth;
+  uint8_t* up;      /* up[v] = 1: v has a neighbour one level closer to the root */
+  int64_t bad;
+} echk_t;
+static void echk_edges(void* c, int tid, int T) {
+  echk_t* s = (echk_t*)c;
+  const int64_t a = s->m * tid / T, b = s->m * (tid + 1) / T;
+  for (int64_t i = a; i < b; ++i) {
+    const int32_t u = s->src[i], v = s->dst[i];
+    const int32_t du = s->depth[u], dv = s->depth[v];
+    if ((du == INT_MAX) != (dv == INT_MAX)) { __atomic_store_n(&s->bad, du == INT_MAX ? u : v, __ATOMIC_RELAXED); return; }
+    if (du == INT_MAX) continue;
+    if (du - dv > 1 || dv - du > 1) { __atomic_store_n(&s->bad, du > dv ? u : v, __ATOMIC_RELAXED); return; }
+    if (du + 1 == dv) s->up[v] = 1;        /* racing stores of the same value */
+    else if (dv + 1 == du) s->up[u] = 1;
+  }
+}
+static void echk_vertices(void* c, int tid, int T) {
+  echk_t* s = (echk_t*)c;
+  const int64_t a = s->n * tid / T, b = s->n * (tid + 1) / T;
+  for (int64_t v = a; v < b; ++v) {
+    const int32_t d = s->depth[v];
+    if (d == INT_MAX) continue;
+    if (d < 0 || (d == 0) != (v == s->root) || (v != s->root && !s->up[v])) { __atomic_store_n(&s->bad, v, __ATOMIC_RELAXED); return; }
+  }
+}
+int64_t oracle_check_depth_by_edges(int64_t n, int64_t m, const int32_t* src, const int32_t* dst, int64_t root,
+                                    const int32_t* depth, int threads) {
+  if (root < 0 || root >= n) return ORACLE_ERR_RANGE - 100;
+  echk_t s = {n, m, root, src, dst, depth, (uint8_t*)calloc((size_t)(n > 0 ? n : 1), 1), -1};
+  if (!s.up) return ORACLE_ERR_NOMEM - 100;
+  if (depth[root] != 0) s.bad = root;
+  if (s.bad < 0) run_on_threads(echk_edges, &s, threads);
+  if (s.bad < 0) run_on_threads(echk_vertices, &s, threads);
+  free(s.up);
+  return s.bad;
+}
+
+/* bfsCPU (bfs.cu:923-945) stopped after it has scanned at least `max_entries` adjacency entries: a
+ * BOUNDED SAMPLE of one serial search for graphs where a whole one takes minutes (bench.py
+ * --impl reference at scale >= 26).  Same loop as oracle_bfs_serial; depth is complete only if the
+ * return value (entries scanned) is below max_entries.  *reached_out = vertices dequeued + queued. */
+int64_t oracle_bfs_serial_bounded(int64_t n, const int64_t* offsets, const int32_t* sizes, const int32_t* adj,
+                                  int64_t start, int32_t* depth, int64_t max_entries, int64_t* reached_out) {
+  for (int64_t v = 0; v < n; ++v) depth[v] = INT_MAX;
+  if (start < 0 || start >= n) return ORACLE_ERR_RANGE;
+  uint8_t* visited = (uint8_t*)calloc((size_t)n, 1);
+  int32_t* q = (int32_t*)malloc((size_t)n * sizeof(int32_t));
+  if (!visited || !q) { free(visited); free(q); return ORACLE_ERR_NOMEM; }
+  int64_t head = 0, tail = 0, scanned = 0;
+  depth[start] = 0;
+  visited[start] = 1;
+  q[tail++] = (int32_t)start;
+  while (head < tail && scanned < max_entries) {
+    const int32_t u = q[head++];
+    const int64_t b = offsets[u], e = b + sizes[u];
+    for (int64_t i = b; i < e; ++i) {
+      const int32_t v = adj[i];
+      if (!visited[v]) {
+        visited[v] = 1;
+        depth[v] = depth[u] + 1;
+        q[tail++] = v;
+      }
+    }
+    scanned += e - b;
+  }
+  free(visited);
+  free(q);
+  if (reached_out) *reached_out = tail;
+  return scanned;
+}

@@ -51,9 +51,44 @@ def test_harmonic_mean():
 
 def test_workload_defaults_follow_the_gpu_count(monkeypatch, capsys):
     import sys
-    for gpus, want_kind, want_scale in ((1, "rmat", 22), (2, "kron", 23), (8, "kron", 25)):
+    for gpus, want_kind, want_scale in ((1, "rmat", 24), (2, "kron", 25), (4, "kron", 26), (8, "kron", 27)):
         seen = {}
-        monkeypatch.setattr(bench, "run_reference_arm", lambda args: seen.update(kind=args.kind, scale=args.scale))
+        monkeypatch.setattr(bench, "run_reference_arm", lambda args: seen.update(kind=args.kind, scale=args.scale, legacy=args.legacy_scale))
         monkeypatch.setattr(sys, "argv", ["bench.py", "--impl", "reference", "--gpus", str(gpus)])
         bench.main()
         assert (seen["kind"], seen["scale"]) == (want_kind, want_scale)
+        assert seen["legacy"] == want_scale - 2  # round 1's sizes ride along under rmat22 / weak22
+
+
+def test_both_arms_print_the_same_config():
+    import argparse
+    a = argparse.Namespace(kind="kron", scale=26, ef=16, seed=1, root_seed=2, mode="do", engine="fused", no_dedup=False,
+                           multi_engine=0, gpus=4)
+    c = bench.workload_config(a)
+    assert "n=67108864, m=1073741824" in c["workload"] and c["multi_engine"] == "peer-memory"
+    a.gpus, a.kind, a.scale = 1, "grid", 24
+    assert "n=16777216, m=33546240" in bench.workload_config(a)["workload"]
+
+
+def test_reference_arm_runs_end_to_end_on_a_small_graph(monkeypatch, capsys):
+    import json
+    import sys
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--impl", "reference", "--kind", "rmat", "--scale", "12", "--steps", "3",
+                                      "--warmup", "1", "--cpu-budget", "5"])
+    bench.main()
+    line = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["value"] > 0 and line["steps"] == 3
+    assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["e2e"]["value"] == line["value"]
+
+
+def test_reference_arm_falls_back_to_the_bounded_port(monkeypatch, capsys):
+    # what runs when 2m >= 2^31 (the reference's int offsets overflow): the 64-bit port, stopped early
+    import json
+    import sys
+    monkeypatch.setattr(oracle, "ref_available", lambda: False)
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--impl", "reference", "--kind", "kron", "--scale", "13", "--steps", "2",
+                                      "--warmup", "1", "--cpu-budget", "2"])
+    bench.main()
+    line = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert line["cpu_baseline"]["kind"] == "port" and line["value"] > 0
+    assert "stopped after" in line["cpu_baseline"]["sample"]

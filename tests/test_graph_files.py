@@ -77,6 +77,35 @@ def test_reference_format_and_errors(b2, graph, tmp_path):
     assert e.value.code == -2
 
 
+def test_crafted_headers_are_format_errors_not_allocations(b2, tmp_path):
+    import struct
+    # binary cache whose edge count would wrap the size check (m * 8 overflows 64 bits)
+    c = tmp_path / "wrap.cache"
+    c.write_bytes(b"B2BFSEDG" + struct.pack("<qq", 8, (1 << 61) + 1) + b"\0" * 64)
+    with pytest.raises(b2.B2BfsError) as e:
+        b2.read_graph_file(str(c), b2.FORMAT_CACHE)
+    assert e.value.code == -3
+    # binary cache with an id outside [0, n)
+    c.write_bytes(b"B2BFSEDG" + struct.pack("<qq", 4, 2) + struct.pack("<4i", 0, 1, 2, 9))
+    with pytest.raises(b2.B2BfsError) as e:
+        b2.read_graph_file(str(c), b2.FORMAT_CACHE)
+    assert e.value.code == -4 and "9" in str(e.value)
+    c.write_bytes(b"B2BFSEDG" + struct.pack("<qq", 4, 2) + struct.pack("<4i", 0, 1, 2, -1))
+    with pytest.raises(b2.B2BfsError) as e:
+        b2.read_graph_file(str(c), b2.FORMAT_CACHE)
+    assert e.value.code == -4
+    # a well-formed cache still loads
+    c.write_bytes(b"B2BFSEDG" + struct.pack("<qq", 4, 2) + struct.pack("<4i", 0, 1, 2, 3))
+    n, s, d = b2.read_graph_file(str(c), b2.FORMAT_CACHE)
+    assert (n, s.tolist(), d.tolist()) == (4, [0, 1], [2, 3])
+    # reference-format header promising 2^40 pairs in a 20-byte file: FORMAT, not NOMEM
+    t = tmp_path / "huge.txt"
+    t.write_text("5 1099511627776\n0 1\n")
+    with pytest.raises(b2.B2BfsError) as e:
+        b2.read_graph_file(str(t), b2.FORMAT_REFERENCE)
+    assert e.value.code == -3 and "too short" in str(e.value)
+
+
 @pytest.mark.gpu
 def test_formats_load_the_same_graph_on_the_gpu(b2, graph, tmp_path):
     n, s, d = graph

@@ -199,3 +199,67 @@ def test_multicore_port_equals_serial(kind, scale):
         want = oracle.bfs_serial(g, root)
         for threads in (1, 3, 0):
             assert oracle.check_output(oracle.bfs_parallel(g, root, threads), want) == -1
+
+
+@pytest.mark.parametrize("kind,scale", [(oracle.GEN_RMAT, 12), (oracle.GEN_KRON, 11), (oracle.GEN_GRID, 8)])
+def test_parallel_csr_builder_holds_the_same_rows(kind, scale):
+    n, src, dst = oracle.generate_edges(kind, scale, 8, 5)
+    g = oracle.build_csr(n, src, dst)
+    p = oracle.build_csr_parallel(n, src, dst, threads=4)
+    assert np.array_equal(g.offsets, p.offsets) and np.array_equal(g.sizes, p.sizes)
+    for v in list(range(0, n, max(1, n // 200))) + [int(np.argmax(g.sizes))]:
+        a, b = g.offsets[v], g.offsets[v] + g.sizes[v]
+        assert sorted(g.adj[a:b].tolist()) == sorted(p.adj[a:b].tolist())
+    root = int(np.argmax(g.sizes))
+    assert oracle.check_output(oracle.bfs_serial(p, root), oracle.bfs_serial(g, root)) == -1
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_edge_rule_check_accepts_reference_depths_on_golden(name):
+    path, gold = load_golden(name)
+    n, src, dst = oracle.read_edge_file(path)
+    for s in gold["searches"]:
+        assert oracle.check_depth_by_edges(n, src, dst, s["root"], np.array(s["depth"], np.int32)) == -1
+
+
+def test_edge_rule_check_rejects_every_kind_of_wrong_depth():
+    n, src, dst = oracle.generate_edges(oracle.GEN_RMAT, 10, 8, 3)
+    g = oracle.build_csr(n, src, dst)
+    root = int(np.argmax(g.sizes))
+    good = oracle.bfs_serial(g, root)
+    assert oracle.check_depth_by_edges(n, src, dst, root, good, threads=3) == -1
+    reached = np.flatnonzero((good != INT_MAX) & (good > 0))
+    rng = np.random.default_rng(0)
+    for v in rng.choice(reached, 12, replace=False):
+        for delta in (+1, -1):
+            bad = good.copy()
+            bad[v] += delta   # too deep: rule 3 or 2 trips; too shallow: rule 2 or 3 trips
+            assert oracle.check_depth_by_edges(n, src, dst, root, bad) != -1, (v, delta)
+        bad = good.copy()
+        bad[v] = INT_MAX      # a reachable vertex reported unreached: rule 2
+        assert oracle.check_depth_by_edges(n, src, dst, root, bad) != -1
+    iso = np.flatnonzero(good == INT_MAX)
+    if len(iso):
+        bad = good.copy()
+        bad[iso[0]] = 3       # an unreachable vertex given a depth: rule 2 (has edges) or rule 3 (has none)
+        assert oracle.check_depth_by_edges(n, src, dst, root, bad) != -1
+    bad = good.copy()
+    bad[root] = 1
+    assert oracle.check_depth_by_edges(n, src, dst, root, bad) != -1
+    # all depths shifted by one keeps every edge rule but breaks the root rule
+    bad = np.where(good == INT_MAX, INT_MAX, good + 1).astype(np.int32)
+    assert oracle.check_depth_by_edges(n, src, dst, root, bad) != -1
+
+
+def test_bounded_serial_search_is_a_prefix_of_the_full_one():
+    n, src, dst = oracle.generate_edges(oracle.GEN_KRON, 12, 16, 1)
+    g = oracle.build_csr(n, src, dst)
+    root = int(np.argmax(g.sizes))
+    full = oracle.bfs_serial(g, root)
+    d, scanned, reached = oracle.bfs_serial_bounded(g, root, 1 << 60)
+    assert oracle.check_output(d, full) == -1 and scanned == oracle.reach_stats(g, full)[1]
+    assert reached == oracle.reach_stats(g, full)[0]
+    d, scanned, reached = oracle.bfs_serial_bounded(g, root, 5000)
+    assert 5000 <= scanned < 5000 + int(g.sizes.max()) + 1 and reached <= oracle.reach_stats(g, full)[0]
+    seen = d != INT_MAX
+    assert np.array_equal(d[seen], full[seen])  # whatever it labelled is labelled correctly

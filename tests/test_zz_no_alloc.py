@@ -47,6 +47,7 @@ def test_noalloc_matches_handle_based_search_twice_in_a_row(b2, kind, scale, ef)
             got_depth = d_depth.cpu().numpy()
             got_parent = d_parent.cpu().numpy()
             assert oracle.check_output(got_depth, want_depth) == -1
+            assert oracle.check_output(got_depth, oracle.bfs_serial(g, root)) == -1  # and the oracle directly
             assert levels == st["levels"]
             # parents may legitimately differ between two valid trees; both must satisfy the rules
             assert oracle.validate_tree(g, root, got_depth, got_parent) == (0, -1)
@@ -64,3 +65,25 @@ def test_noalloc_rejects_graphs_beyond_the_built_in_scratch(b2):
     assert e.value.code == -4
     with pytest.raises(b2.B2BfsError):
         b2.search_noalloc(0, 8, 0, d.data_ptr(), d.data_ptr(), 9, out.data_ptr(), out.data_ptr())  # bad source
+
+
+def test_noalloc_takes_no_device_memory_after_its_set_up_call(b2):
+    """The promise to callers who cannot allocate: once the first (set-up) call on a device is behind
+    us, a search leaves the amount of free device memory exactly where it was."""
+    with b2.Bfs(0) as h:
+        h.generate(0, 12, 8, 7)
+        n = h.num_vertices
+        rowptr, col, d_rowptr, d_col = _device_csr(b2, h)
+        d_depth = torch.empty(n, dtype=torch.int32, device="cuda")
+        d_parent = torch.empty(n, dtype=torch.int32, device="cuda")
+        root = int(np.argmax(np.diff(rowptr)))
+        call = lambda: b2.search_noalloc(0, n, len(col), d_rowptr.data_ptr(), d_col.data_ptr(), root,
+                                         d_depth.data_ptr(), d_parent.data_ptr())
+        call()  # set-up call (a no-op here when the tests above already ran)
+        torch.cuda.synchronize()
+        free_before, _ = torch.cuda.mem_get_info(0)
+        for _ in range(3):
+            call()
+        torch.cuda.synchronize()
+        free_after, _ = torch.cuda.mem_get_info(0)
+        assert free_after == free_before
