@@ -88,6 +88,10 @@ def lib() -> C.CDLL:
             "b2bfs_copy_csr": ([vp, vp, i32p], C.c_int),
             "b2bfs_run": ([vp, i64, i32p, i32p, C.POINTER(Stats)], C.c_int),
             "b2bfs_run_device": ([vp, i64, C.POINTER(Stats)], C.c_int),
+            "b2bfs_run_slice": ([vp, i64, i32p, i32p, C.POINTER(Stats)], C.c_int),
+            "b2bfs_local_range": ([vp, C.POINTER(i64), C.POINTER(i64)], C.c_int),
+            "b2bfs_host_register": ([vp, i64], C.c_int),
+            "b2bfs_host_unregister": ([vp], C.c_int),
             "b2bfs_device_depth": ([vp, C.POINTER(vp)], C.c_int),
             "b2bfs_device_parent": ([vp, C.POINTER(vp)], C.c_int),
             "b2bfs_last_trace": ([vp, vp, vp, vp, C.c_int], C.c_int),
@@ -168,6 +172,36 @@ class PinnedArray:
             self.array = None
             lib().b2bfs_host_free(self._p)
             self._p = C.c_void_p()
+
+
+class SharedPinnedArray:
+    """n x dtype in a POSIX shared-memory file that every rank of a node maps and page-locks: ranks
+    write their slices of a result into it over their own PCIe links (Bfs.run_slice) and any rank can
+    read the whole array afterwards.  Rank 0 creates (and finally unlinks) the file."""
+
+    def __init__(self, name: str, n: int, dtype=np.int32, create: bool = False):
+        self.path = os.path.join("/dev/shm", name)
+        self.nbytes = max(int(n) * np.dtype(dtype).itemsize, 1)
+        self.created = create
+        if create:
+            with open(self.path, "wb") as f:
+                f.truncate(self.nbytes)
+        self._mm = np.memmap(self.path, dtype=np.uint8, mode="r+", shape=(self.nbytes,))
+        self._mm[::4096] = 0  # touch every page before locking it
+        self.array = self._mm.view(dtype)[:int(n)]
+        self._registered = lib().b2bfs_host_register(self._mm.ctypes.data, self.nbytes) == 0
+
+    def free(self):
+        if self._mm is not None:
+            if self._registered:
+                lib().b2bfs_host_unregister(self._mm.ctypes.data)
+            self.array = None
+            self._mm = None
+            if self.created:
+                try:
+                    os.unlink(self.path)
+                except OSError:
+                    pass
 
 
 class Bfs:
@@ -305,6 +339,19 @@ class Bfs:
         st = Stats()
         self._check(lib().b2bfs_run(self._h, int(src), depth_out.ctypes.data if depth_out is not None else None,
                                     None, C.byref(st)))
+        return st.as_dict()
+
+    def local_range(self):
+        """(first vertex, count) of the rows this rank owns (all of them on a single GPU)."""
+        a, b = C.c_int64(), C.c_int64()
+        self._check(lib().b2bfs_local_range(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def run_slice(self, src: int, depth_slice, parent_slice=None):
+        """Multi-rank: every rank calls this; each receives only its own rows (no cross-GPU gather)."""
+        st = Stats()
+        self._check(lib().b2bfs_run_slice(self._h, int(src), depth_slice.ctypes.data,
+                                          parent_slice.ctypes.data if parent_slice is not None else None, C.byref(st)))
         return st.as_dict()
 
     def run_device(self, src: int):

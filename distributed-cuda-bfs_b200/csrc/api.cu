@@ -25,7 +25,7 @@ struct b2bfs {
   std::string err;
   // options
   int dedup = 1, mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED;
-  int alpha = 14, beta = 24, keep_edges = 1, gather_parent = 1, hub_first = 1;
+  int alpha = 14, beta = 24, gamma = 24, xvariant = 0, keep_edges = 1, gather_parent = 1, hub_first = 1;
   // graph
   bool has_graph = false;
   int64_t n = 0, m = 0;
@@ -49,7 +49,6 @@ struct b2bfs {
   unsigned char* xregion = nullptr;
   unsigned char* xpeer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   int grid_multi = 0;
-  unsigned long long search_seq = 0;
 };
 
 static thread_local std::string g_create_error;
@@ -258,6 +257,8 @@ static BfsParams make_params(const b2bfs* h) {
   p.tn.mode = h->mode;
   p.tn.alpha = h->alpha;
   p.tn.beta = h->beta;
+  p.tn.gamma = h->gamma;
+  p.tn.xvariant = h->xvariant;
   return p;
 }
 
@@ -457,6 +458,8 @@ int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
   else if (k == "multi_engine" && (value == 0 || value == 1)) h->multi_engine = (int)value;
   else if (k == "alpha" && value >= 1 && value <= (1 << 20)) h->alpha = (int)value;
   else if (k == "beta" && value >= 1 && value <= (1 << 20)) h->beta = (int)value;
+  else if (k == "gamma" && value >= 0 && value <= (1 << 20)) h->gamma = (int)value;
+  else if (k == "xvariant" && (value == 0 || value == 1)) h->xvariant = (int)value;
   else return fail(h, B2BFS_ERR_ARG, "unknown option or value out of range: " + k);
   return B2BFS_OK;
 }
@@ -471,6 +474,8 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   else if (k == "engine") *value = h->engine;
   else if (k == "alpha") *value = h->alpha;
   else if (k == "beta") *value = h->beta;
+  else if (k == "gamma") *value = h->gamma;
+  else if (k == "xvariant") *value = h->xvariant;
   else if (k == "grid") *value = h->grid;
   else if (k == "gather_parent") *value = h->gather_parent;
   else if (k == "multi_engine") *value = (h->world > 1 && h->p2p_ready && h->multi_engine == 0) ? 0 : 1;
@@ -633,8 +638,10 @@ int b2bfs_copy_csr(b2bfs_t* h, int64_t* rowptr_out, int32_t* col_out) {
   return B2BFS_OK;
 }
 
+enum GatherMode { kGatherNone = 0, kGatherAll = 1, kGatherSlice = 2 };
+
 static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent_out, b2bfs_stats* stats,
-                    bool gather) {
+                    GatherMode gather) {
   if (!h) return fail(h, B2BFS_ERR_ARG, "null handle");
   if (!h->has_graph) return fail(h, B2BFS_ERR_STATE, "b2bfs_run: no graph resident");
   if (src < 0 || src >= h->n) return fail(h, B2BFS_ERR_ARG, "b2bfs_run: source vertex outside [0, vertex_num)");
@@ -646,16 +653,27 @@ static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent
   MultiResult mr;
   API_CUDA(h, cudaEventRecord(h->ev0, h->stream));
   const bool p2p = multi && p.s.xbase[0] != nullptr;
-  Status s = p2p ? run_fused_multi(p, src, (++h->search_seq) << 32, h->grid_multi, h->stream, &mr.launches)
+  Status s = p2p ? run_fused_multi(p, src, h->grid_multi, h->stream, &mr.launches)
            : multi ? run_multi(p, h->mc, src, h->grid, h->stream, &mr)
            : (h->engine == B2BFS_ENGINE_FUSED) ? run_fused(p, src, h->grid, h->stream, &launches)
                                                : run_stepwise(p, src, h->grid, h->stream, h->pinned_ctl, &launches);
   if (!s.ok()) return fail(h, s);
   API_CUDA(h, cudaEventRecord(h->ev1, h->stream));
   int64_t d2h = 0;
-  if (multi) {
+  if (multi && gather == kGatherSlice) {
+    // this rank's rows only, over this GPU's own PCIe link: no cross-GPU gather at all
     launches = mr.launches;
-    if (gather) {  // collective: every rank takes part, whoever passed a buffer gets all n entries
+    if (depth_out && h->nloc > 0) {
+      API_CUDA(h, cudaMemcpyAsync(depth_out, h->sv.depth, (size_t)h->nloc * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+      d2h += h->nloc * (int64_t)sizeof(int32_t);
+    }
+    if (parent_out && h->nloc > 0) {
+      API_CUDA(h, cudaMemcpyAsync(parent_out, h->sv.parent, (size_t)h->nloc * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+      d2h += h->nloc * (int64_t)sizeof(int32_t);
+    }
+  } else if (multi) {
+    launches = mr.launches;
+    if (gather == kGatherAll) {  // collective: every rank takes part, whoever passed a buffer gets all n entries
       int rc = gather_i32(h, h->sv.depth, depth_out, &d2h);
       if (rc) return rc;
       if (h->gather_parent) {
@@ -708,11 +726,23 @@ static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent
 int b2bfs_run(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent_out, b2bfs_stats* stats) {
   if (h && h->world == 1 && !depth_out)
     return fail(h, B2BFS_ERR_ARG, "b2bfs_run: depth_out is null (use b2bfs_run_device to keep results in HBM)");
-  return run_impl(h, src, depth_out, parent_out, stats, true);
+  return run_impl(h, src, depth_out, parent_out, stats, kGatherAll);
 }
 
 int b2bfs_run_device(b2bfs_t* h, int64_t src, b2bfs_stats* stats) {
-  return run_impl(h, src, nullptr, nullptr, stats, false);
+  return run_impl(h, src, nullptr, nullptr, stats, kGatherNone);
+}
+
+int b2bfs_run_slice(b2bfs_t* h, int64_t src, int32_t* depth_slice_out, int32_t* parent_slice_out, b2bfs_stats* stats) {
+  if (h && !depth_slice_out) return fail(h, B2BFS_ERR_ARG, "b2bfs_run_slice: depth_slice_out is null");
+  return run_impl(h, src, depth_slice_out, parent_slice_out, stats, h && h->world > 1 ? kGatherSlice : kGatherAll);
+}
+
+int b2bfs_local_range(const b2bfs_t* h, int64_t* first_vertex, int64_t* count) {
+  if (!h || !first_vertex || !count || !h->has_graph) return B2BFS_ERR_ARG;
+  *first_vertex = h->vbase;
+  *count = h->nloc;
+  return B2BFS_OK;
 }
 
 int b2bfs_device_depth(const b2bfs_t* h, const int32_t** depth_dev) {
@@ -732,6 +762,7 @@ int b2bfs_last_trace(b2bfs_t* h, int32_t* level_out, int32_t* phase_out, double*
   if (cudaMemcpy(h->pinned_ctl, h->sv.ctl, sizeof(Control), cudaMemcpyDeviceToHost) != cudaSuccess) return B2BFS_ERR_CUDA;
   const Control* c = h->pinned_ctl;
   int n = c->trace_len < cap ? c->trace_len : cap;
+  if (n > kTraceCap) n = kTraceCap;
   for (int i = 0; i < n; ++i) {
     level_out[i] = c->trace[i].level;
     phase_out[i] = c->trace[i].phase;
@@ -745,6 +776,13 @@ int b2bfs_host_alloc(void** p, int64_t bytes) {
   return cudaMallocHost(p, (size_t)(bytes > 0 ? bytes : 1)) == cudaSuccess ? B2BFS_OK : B2BFS_ERR_NOMEM;
 }
 int b2bfs_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? B2BFS_OK : B2BFS_ERR_CUDA; }
+int b2bfs_host_register(void* p, int64_t bytes) {
+  if (!p || bytes <= 0) return B2BFS_ERR_ARG;
+  const cudaError_t e = cudaHostRegister(p, (size_t)bytes, cudaHostRegisterPortable);
+  if (e != cudaSuccess) cudaGetLastError();
+  return e == cudaSuccess ? B2BFS_OK : (e == cudaErrorMemoryAllocation ? B2BFS_ERR_NOMEM : B2BFS_ERR_CUDA);
+}
+int b2bfs_host_unregister(void* p) { return cudaHostUnregister(p) == cudaSuccess ? B2BFS_OK : B2BFS_ERR_CUDA; }
 
 int b2bfs_destroy(b2bfs_t* h) {
   if (!h) return B2BFS_OK;

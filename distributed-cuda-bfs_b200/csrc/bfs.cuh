@@ -24,8 +24,7 @@ void launch_queue_to_bitmap(const BfsParams& p, const LoopState& st, int grid, c
 void launch_bitmap_to_queue(const BfsParams& p, const LoopState& st, int grid, cudaStream_t s);
 void launch_pack_stats(const BfsParams& p, int slot, unsigned long long* out, cudaStream_t s);
 
-Status run_fused_multi(const BfsParams& p, int64_t src, unsigned long long epoch_base, int grid, cudaStream_t stream,
-                       int64_t* launches);
+Status run_fused_multi(const BfsParams& p, int64_t src, int grid, cudaStream_t stream, int64_t* launches);
 Status multi_grid_size(int device, int* grid_out);
 
 Status run_reach_stats(const BfsParams& p, const uint32_t* orig_deg, cudaStream_t stream, int64_t* launches);

@@ -212,6 +212,7 @@ __host__ __device__ inline LoopState initial_state(const BfsParams& p, int64_t s
   st.cur_wide = wide ? (unsigned)((src_degree + kChunk - 1) / kChunk) : 0u;
   st.prev_nf = 1;
   st.unexplored = (unsigned long long)(p.g.entries - src_degree);
+  st.frontier_edges = (unsigned long long)src_degree;
   st.td_levels = st.bu_levels = 0;
   return st;
 }
@@ -267,7 +268,7 @@ __device__ __forceinline__ void remote_flush(const BfsParams& p, RemoteStage& rs
 template <bool kMulti>
 __device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpStage& sg, RemoteStage* rs,
                                           const int32_t (&v)[4], const int32_t (&u)[4], const bool (&valid)[4],
-                                          unsigned long long& edges_acc, bool mark) {
+                                          unsigned long long& edges_acc, bool mark, bool claim_only) {
   uint32_t word[4];
   bool c[4], local[4];
   int32_t vl[4];
@@ -295,6 +296,22 @@ __device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpSta
   }
 #pragma unroll
   for (int k = 0; k < 4; ++k) c[k] = c[k] && !((word[k] >> (v[k] & 31)) & 1u);
+  if (claim_only) {  // no work lists for the next level: claim, mark, count (edges_acc counts CLAIMS here)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (c[k]) {
+        if (local[k]) {
+          p.s.depth[vl[k]] = level + 1;
+          p.s.parent[vl[k]] = u[k];
+          edges_acc++;
+          atomicOr(&p.s.bitmap[0][(uint32_t)vl[k] >> 5], 1u << (vl[k] & 31));
+        } else if (kMulti) {
+          rs->pair[atomicAdd(&rs->cnt, 1)] = make_int2(v[k], u[k]);
+        }
+      }
+    }
+    return;
+  }
   int64_t d[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k)
@@ -319,7 +336,7 @@ __device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpSta
 
 template <bool kMulti>
 __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStage* stage, int bid, int nb,
-                                               RemoteStage* rstage = nullptr, bool mark = false) {
+                                               RemoteStage* rstage = nullptr, bool mark = false, bool claim_only = false) {
   const int level = st.level;
   const int32_t* q = p.s.queue[level & 1];
   const int2* wq = p.s.wideq[level & 1];
@@ -381,7 +398,7 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
           valid[j] = k < total;
           v[j] = valid[j] ? __ldg(p.g.col + ors + (k - oe)) : 0;
         }
-        td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark);
+        td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only);
         stage_flush(sg, ns, nq, nwq, false);
         if (kMulti) remote_flush(p, *rst, false);
       }
@@ -399,7 +416,7 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
           const int32_t uu[4] = {u + vbase, u + vbase, u + vbase, u + vbase};
           const bool valid[4] = {base >= rs, base + 1 >= rs && base + 1 < re, base + 2 >= rs && base + 2 < re,
                                  base + 3 >= rs && base + 3 < re};
-          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark);
+          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only);
         }
         stage_flush(sg, ns, nq, nwq, false);
         if (kMulti) remote_flush(p, *rst, false);
@@ -408,13 +425,16 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
   }
   stage_flush(sg, ns, nq, nwq, true);
   if (kMulti) remote_flush(p, *rst, true);
-  block_accumulate(edges_acc, &ns->edges);
+  block_accumulate(edges_acc, claim_only ? &ns->bu_count : &ns->edges);
 }
 
 // Multi-rank: claim the (vertex, parent) pairs other ranks discovered in this rank's rows and queue
-// the winners for the next level (same slot counters and staging as the local discoveries).
+// the winners for the next level (same slot counters and staging as the local discoveries).  The
+// pairs sit in `nb` buckets of `stride` pairs each (bucket s holds counts[s] of them); all buckets
+// are walked in ONE pass, so the phase pays its staging flush and its block reduction once.
 __device__ __forceinline__ void phase_apply_remote(const BfsParams& p, const LoopState& st, WarpStage* stage,
-                                                   const int2* recv, int64_t count) {
+                                                   const int2* recv, int64_t stride, const unsigned int* counts, int nb,
+                                                   bool mark = false, bool claim_only = false) {
   const int level = st.level;
   int32_t* nq = p.s.queue[(level + 1) & 1];
   int2* nwq = p.s.wideq[(level + 1) & 1];
@@ -423,26 +443,35 @@ __device__ __forceinline__ void phase_apply_remote(const BfsParams& p, const Loo
   if (lane_id() == 0) { sg.ncnt = 0; sg.wcnt = 0; }
   __syncwarp();
   unsigned long long edges_acc = 0;
+  int64_t count = 0;
+  for (int b = 0; b < nb; ++b) count += counts[b];
   const int64_t nthreads = (int64_t)gridDim.x * kBlock;
   const int64_t rounds = (count + nthreads - 1) / nthreads;
   for (int64_t r = 0; r < rounds; ++r) {  // warp-uniform trip count
-    const int64_t i = r * nthreads + (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    int64_t i = r * nthreads + (int64_t)blockIdx.x * kBlock + threadIdx.x;
     if (i < count) {
-      const int2 e = __ldcg(recv + i);  // written by another GPU (or by NCCL): read at L2
+      int b = 0;
+      while (i >= (int64_t)counts[b]) { i -= counts[b]; ++b; }
+      const int2 e = __ldcg(recv + (int64_t)b * stride + i);  // written by another GPU (or by NCCL): read at L2
       const int32_t vl = e.x - (int32_t)p.g.vbase;
       const uint32_t w = (uint32_t)vl >> 5, bit = 1u << (vl & 31);
       if ((uint32_t)vl < (uint32_t)p.g.n && !(p.s.visited[w] & bit) && !(atomicOr(&p.s.visited[w], bit) & bit)) {
         p.s.depth[vl] = level + 1;
         p.s.parent[vl] = e.y;
-        const int64_t d = __ldg(p.g.rowptr + vl + 1) - __ldg(p.g.rowptr + vl);
-        edges_acc += (unsigned long long)d;
-        route_vertex(sg, vl, d);
+        if (claim_only) {
+          edges_acc++;  // counts claims
+        } else {
+          const int64_t d = __ldg(p.g.rowptr + vl + 1) - __ldg(p.g.rowptr + vl);
+          edges_acc += (unsigned long long)d;
+          route_vertex(sg, vl, d);
+        }
+        if (mark) atomicOr(&p.s.bitmap[0][w], bit);
       }
     }
     stage_flush(sg, ns, nq, nwq, false);
   }
   stage_flush(sg, ns, nq, nwq, true);
-  block_accumulate(edges_acc, &ns->edges);
+  block_accumulate(edges_acc, claim_only ? &ns->bu_count : &ns->edges);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -753,9 +782,9 @@ __device__ __forceinline__ void phase_bitmap_to_queue(const BfsParams& p, const 
 // stepwise engine: one kernel per phase
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock) search_init_kernel(BfsParams p, int64_t src) { phase_init(p, src); }
-__global__ void __launch_bounds__(kBlock) top_down_kernel(BfsParams p, LoopState st) {
+__global__ void __launch_bounds__(kBlock) top_down_kernel(BfsParams p, LoopState st, bool claim_only) {
   __shared__ WarpStage stage[kWarpsPerBlock];
-  phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x);
+  phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x, nullptr, claim_only, claim_only);
 }
 __global__ void __launch_bounds__(kBlock) bottom_up_kernel(BfsParams p, LoopState st) {
   __shared__ WarpStage stage[kWarpsPerBlock];
@@ -779,7 +808,8 @@ __global__ void __launch_bounds__(kBlock) top_down_multi_kernel(BfsParams p, Loo
 }
 __global__ void __launch_bounds__(kBlock) apply_remote_kernel(BfsParams p, LoopState st, const int2* recv, int64_t count) {
   __shared__ WarpStage stage[kWarpsPerBlock];
-  phase_apply_remote(p, st, stage, recv, count);
+  const unsigned int counts[1] = {(unsigned int)count};  // NCCL delivered the pairs back to back: one bucket
+  phase_apply_remote(p, st, stage, recv, 0, counts, 1);
 }
 // one 16-word record per rank per exchange: [0] narrow queue tail, [1] wide tail, [2] degree sum,
 // [3] bottom-up finds, [4] source degree, [8 + d] pairs staged for rank d
@@ -856,20 +886,27 @@ __device__ __forceinline__ void group_barrier(unsigned long long* counter, unsig
   __syncthreads();
 }
 
-__device__ __forceinline__ void trace_mark(Control* c, int& n, int level, int phase) {
-  if (blockIdx.x == 0 && threadIdx.x == 0 && n < kTraceCap) {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    c->trace[n].level = level;
-    c->trace[n].phase = phase;
-    c->trace[n].t_ns = t;
-    c->trace_len = ++n;
+// one record per call, from whichever thread calls (slots are handed out by an atomic counter that
+// phase_init's caller zeroes before the first mark of a search)
+__device__ __forceinline__ void trace_put(Control* c, int level, int phase) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  const int i = atomicAdd(&c->trace_len, 1);
+  if (i < kTraceCap) {
+    c->trace[i].level = level;
+    c->trace[i].phase = phase;
+    c->trace[i].t_ns = t;
   }
+}
+__device__ __forceinline__ void trace_mark(Control* c, int& n, int level, int phase) {
+  (void)n;
+  if (blockIdx.x == 0 && threadIdx.x == 0) trace_put(c, level, phase);
 }
 
 __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(BfsParams p, int64_t src) {
   __shared__ WarpStage stage[kWarpsPerBlock];
   cg::grid_group grid = cg::this_grid();
+  if (blockIdx.x == 0 && threadIdx.x == 0) p.s.ctl->trace_len = 0;
   phase_init(p, src);
   LoopState st = initial_state(p, __ldg(p.g.rowptr + src + 1) - __ldg(p.g.rowptr + src));
   const int group = min((int)gridDim.x, kGroupBlocks);
@@ -917,13 +954,14 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
     } else {
       const int ph = st.mode == 0 ? 1 : 2;
       marked = st.mode == 0 && p.tn.mode == B2BFS_MODE_DIRECTION_OPT && st.bu_levels == 0 && st.level >= 1;
-      if (st.mode == 0) phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x, nullptr, marked);
+      const bool claim = claim_only_level(st, p.tn);  // implies marked
+      if (st.mode == 0) phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x, nullptr, marked, claim);
       else phase_bottom_up(p, st, stage);
       grid.sync();
-      trace_mark(p.s.ctl, ntrace, st.level, ph);
+      trace_mark(p.s.ctl, ntrace, st.level, claim ? 6 : ph);
       const LevelSlot* ns = &p.s.ctl->slot[(st.level + 1) & 3];
       cv = advance(st, p.tn, p.g.n, ld_volatile(&ns->q_count), ld_volatile(&ns->wide_count),
-                   ld_volatile(&ns->bu_count), ld_volatile(&ns->edges));
+                   ld_volatile(&ns->bu_count), ld_volatile(&ns->edges), claim);
     }
     if (cv == kQueueToBitmap) {
       if (!marked) {  // a marking top-down level has already left the new frontier in bitmap[0]
@@ -976,30 +1014,52 @@ __device__ __forceinline__ volatile unsigned long long* xrecord(const BfsParams&
 }
 
 // All ranks call this the same number of times.  On return sums[0..4] = totals over ranks of
-// (narrow tail, wide tail, degree sum, bottom-up finds, source degree) of `slot`, mine[0..1] = this
+// (narrow tail, wide tail, degree sum, bottom-up finds, source degree) of `slot`, sums[5..6] = this
 // rank's own tails and incoming[s] = pairs rank s staged for this rank.
+//
+// One exchange = one arrival atomic per CTA, one NVLink store burst, one poll:
+//   * every CTA bumps an arrival counter (nth = number of this exchange in the kernel, 1-based; the
+//     host zeroes the counter before the launch);
+//   * the CTA that arrives LAST knows that everything this GPU wrote for its peers during the phase
+//     is on its way (the issuing warps fenced their own peer stores: remote_flush and
+//     push_frontier_slice end with __threadfence_system) and stores this rank's record into every
+//     rank's table, the epoch number last;
+//   * every CTA then polls ITS OWN table until the records of all ranks carry this epoch - nobody
+//     waits for a second, local release step.
+// `epoch` runs on across searches (Control::xepoch), so a slot of the 4-deep record ring is never
+// rewritten while a slower rank may still be reading it: to post epoch e+4 a rank must have
+// completed e+1..e+3, and completing e+1 needs every CTA of every rank to have arrived there, i.e.
+// to have finished reading e.
+__device__ __forceinline__ bool wait_for_records(const BfsParams& p, unsigned long long epoch, int from_rank) {
+  volatile unsigned long long* src = xrecord(p, p.g.rank, epoch, from_rank);
+  const unsigned long long t0 = global_ns();
+  while (src[31] != epoch) {
+    __nanosleep(40);
+    if (global_ns() - t0 > 4000000000ull) {  // 4 s: a peer died or never launched
+      p.s.ctl->error = 1;
+      return false;
+    }
+  }
+  return true;
+}
+
 __device__ __forceinline__ void cross_exchange(const BfsParams& p, unsigned long long epoch, unsigned long long nth,
-                                               int slot, unsigned long long* sums, unsigned int* incoming, int* failed) {
+                                               int slot, unsigned long long* sums, unsigned int* incoming, int* failed,
+                                               int trace_level = -1) {
   __shared__ unsigned long long rec_s[8][16];
+  __shared__ int last_s;
   const int k = p.g.world, me = p.g.rank;
   Control* ctl = p.s.ctl;
-  // ONE grid-wide rendezvous with the cross-GPU step inside it (nth = number of this exchange in the
-  // kernel, 1-based; xarrive/xrelease are zeroed by the host before the launch):
-  // stores to peer memory were already drained by the warps that issued them (remote_flush,
-  // push_frontier_slice end with __threadfence_system): a fence issued later by one thread of CTA 0 is
-  // not known to wait for other SMs' writes still in flight on other NVLink lanes
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence();
-    atomicAdd(&ctl->xarrive, 1ull);
+    __threadfence();  // this CTA's counter atomics and local writes are ordered before its arrival
+    const unsigned long long before = atomicAdd(&ctl->xarrive, 1ull);
+    last_s = (before + 1 == nth * gridDim.x);
+    if (last_s) __threadfence();
   }
-  if (blockIdx.x == 0) {
-    if (threadIdx.x == 0) {
-      const unsigned long long target = nth * gridDim.x;
-      while (ld_volatile(&ctl->xarrive) < target) {}
-      __threadfence();
-    }
-    __syncthreads();  // everything this GPU wrote for its peers during the phase has landed
+  __syncthreads();
+  if (last_s) {
+    if (threadIdx.x == 0 && trace_level >= 0) trace_put(ctl, trace_level, 11);  // every CTA of this GPU has arrived
     if ((int)threadIdx.x < k) {
       const int d = threadIdx.x;
       const LevelSlot* s = &ctl->slot[slot & 3];
@@ -1012,25 +1072,28 @@ __device__ __forceinline__ void cross_exchange(const BfsParams& p, unsigned long
       for (int j = 0; j < 8; ++j) dst[8 + j] = j < k ? ld_volatile(&p.s.send_count[j * 32]) : 0u;
       __threadfence_system();
       dst[31] = epoch;  // arrival flag, after the payload
-      volatile unsigned long long* src = xrecord(p, me, epoch, d);
-      const unsigned long long t0 = global_ns();
-      while (src[31] != epoch) {
-        if (global_ns() - t0 > 4000000000ull) {  // 4 s: a peer died or never launched
-          ctl->error = 1;
-          break;
-        }
-      }
-      __threadfence_system();
     }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      __threadfence();
-      *reinterpret_cast<volatile unsigned long long*>(&ctl->xrelease) = nth;
+    if (p.tn.xvariant == 1) {  // this CTA alone waits for the peers, then releases the others
+      if ((int)threadIdx.x < k) {
+        wait_for_records(p, epoch, threadIdx.x);
+        __threadfence_system();
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        if (trace_level >= 0) trace_put(ctl, trace_level, 12);  // the records of all ranks are here
+        __threadfence();
+        *reinterpret_cast<volatile unsigned long long*>(&ctl->xrelease) = nth;
+      }
     }
   }
-  if (threadIdx.x == 0) {
-    while (ld_volatile(&ctl->xrelease) < nth) {}
-    __threadfence();  // also drops L1 lines that predate what the peers just wrote here
+  if (p.tn.xvariant == 1) {
+    if (threadIdx.x == 0) {
+      while (ld_volatile(&ctl->xrelease) < nth) __nanosleep(20);
+      __threadfence();
+    }
+  } else if ((int)threadIdx.x < k) {
+    wait_for_records(p, epoch, threadIdx.x);
+    __threadfence();  // the peers' payload stores were system-fenced before their flags left
   }
   __syncthreads();
   if ((int)threadIdx.x < k * 16) rec_s[threadIdx.x >> 4][threadIdx.x & 15] = xrecord(p, me, epoch, threadIdx.x >> 4)[threadIdx.x & 15];
@@ -1038,7 +1101,7 @@ __device__ __forceinline__ void cross_exchange(const BfsParams& p, unsigned long
   for (int i = 0; i < 5; ++i) sums[i] = 0;
   for (int r = 0; r < k; ++r) {
     for (int i = 0; i < 5; ++i) sums[i] += rec_s[r][i];
-    incoming[r] = (unsigned int)rec_s[r][8 + me];
+    incoming[r] = r == me ? 0u : (unsigned int)rec_s[r][8 + me];
   }
   sums[5] = rec_s[me][0];
   sums[6] = rec_s[me][1];
@@ -1060,13 +1123,14 @@ __device__ __forceinline__ void push_frontier_slice(const BfsParams& p, int whic
   __threadfence_system();  // the slice is in every peer's memory before this thread reaches the exchange
 }
 
-__global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_kernel(BfsParams p, int64_t src,
-                                                                                      unsigned long long epoch) {
+__global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_kernel(BfsParams p, int64_t src) {
   __shared__ WarpStage stage[kWarpsPerBlock];
   __shared__ RemoteStage rstage[kWarpsPerBlock];
   cg::grid_group grid = cg::this_grid();
   const int k = p.g.world, me = p.g.rank;
   const int64_t src_local = (src / p.g.part == me) ? src - p.g.vbase : -1;
+  unsigned long long epoch = ld_volatile(&p.s.ctl->xepoch);  // exchanges completed by earlier searches (same on all ranks)
+  if (blockIdx.x == 0 && threadIdx.x == 0) p.s.ctl->trace_len = 0;
   {  // reset: local state as on one GPU, plus the replicated `seen` filter
     uint4* s4 = reinterpret_cast<uint4*>(p.s.seen);
     const int64_t n4 = (int64_t)k * p.g.part / 128;
@@ -1091,24 +1155,36 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
   st.cur_wide = ld_volatile(&p.s.ctl->slot[0].wide_count);
   st.prev_nf = 1;
   st.unexplored = p.g.entries_global;  // the source's own degree is noise at this size
+  st.frontier_edges = 0;
   st.td_levels = st.bu_levels = 0;
   int gcur = 0;  // frontier bitmap buffer bottom-up reads
+  const int2* inbox = reinterpret_cast<const int2*>(p.s.xbase[me] + xchg_off_inbox(k, p.g.part));
 
   while (!st.done) {
     unsigned long long nf = 0, mf = 0;
+    bool claim = false;
+    bool pushed = false;  // this level's discoveries already sit in everyone's frontier buffer gcur ^ 1
     if (st.mode == 0) {
-      phase_top_down<true>(p, st, stage, blockIdx.x, gridDim.x, rstage);
+      // a top-down level that may well be the last one before bottom-up leaves the frontier bit of
+      // every discovery behind (as on one GPU) and ships the slice together with exchange #2, so
+      // the switch costs neither a queue->bitmap pass nor an exchange of its own
+      const bool marked = p.tn.mode == B2BFS_MODE_DIRECTION_OPT && st.bu_levels == 0 && st.level >= 1;
+      claim = claim_only_level(st, p.tn);  // implies marked; same decision on every rank (global counters)
+      phase_top_down<true>(p, st, stage, blockIdx.x, gridDim.x, rstage, marked, claim);
       trace_mark(p.s.ctl, ntrace, st.level, 6);
-      cross_exchange(p, ++epoch, ++nth, st.level + 1, sums, incoming, &failed);  // pair counts
+      cross_exchange(p, ++epoch, ++nth, st.level + 1, sums, incoming, &failed, st.level);  // #1: pair counts
       trace_mark(p.s.ctl, ntrace, st.level, 7);
-      const int2* inbox = reinterpret_cast<const int2*>(p.s.xbase[me] + xchg_off_inbox(k, p.g.part));
-      for (int s = 0; s < k; ++s)
-        if (s != me && incoming[s]) phase_apply_remote(p, st, stage, inbox + (int64_t)s * p.s.send_cap, incoming[s]);
-      if (blockIdx.x == 0 && (int)threadIdx.x < p.g.world) p.s.send_count[threadIdx.x * 32] = 0;  // all counts were read above
-      cross_exchange(p, ++epoch, ++nth, st.level + 1, sums, incoming, &failed);  // tails after the arrivals
+      phase_apply_remote(p, st, stage, inbox, p.s.send_cap, incoming, k, marked, claim);
+      if (blockIdx.x == 0 && (int)threadIdx.x < p.g.world) p.s.send_count[threadIdx.x * 32] = 0;  // posted in #1
+      if (marked) {
+        grid.sync();  // bits set by any CTA (local finds and arrivals) are all in bitmap[0]
+        push_frontier_slice(p, gcur ^ 1);
+        pushed = true;
+      }
+      cross_exchange(p, ++epoch, ++nth, st.level + 1, sums, incoming, &failed, st.level);  // #2: tails after the arrivals
       trace_mark(p.s.ctl, ntrace, st.level, 8);
-      nf = sums[0] + sums[1];
-      mf = sums[2];
+      nf = claim ? sums[3] : sums[0] + sums[1];
+      mf = claim ? 0 : sums[2];
       st.cur_q = (unsigned)sums[5];
       st.cur_wide = (unsigned)sums[6];
       st.td_levels++;
@@ -1118,26 +1194,33 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
       grid.sync();  // the slice is complete (late finds are OR-ed in by any CTA)
       trace_mark(p.s.ctl, ntrace, st.level, 9);
       push_frontier_slice(p, gcur ^ 1);
-      cross_exchange(p, ++epoch, ++nth, st.level + 1, sums, incoming, &failed);
+      cross_exchange(p, ++epoch, ++nth, st.level + 1, sums, incoming, &failed, st.level);
       trace_mark(p.s.ctl, ntrace, st.level, 10);
       gcur ^= 1;
       nf = sums[3];
       st.bu_levels++;
     }
     st.unexplored = mf > st.unexplored ? 0ull : st.unexplored - mf;
+    st.frontier_edges = mf;
     st.level++;
+    bool switched = false;
     if (nf == 0 || failed) {
       st.done = 1;
     } else if (st.mode == 0) {
-      if (p.tn.mode == B2BFS_MODE_DIRECTION_OPT && mf > st.unexplored / (unsigned)p.tn.alpha && nf >= st.prev_nf) {
+      if (claim || (p.tn.mode == B2BFS_MODE_DIRECTION_OPT && mf > st.unexplored / (unsigned)p.tn.alpha && nf >= st.prev_nf)) {
         st.mode = 1;
-        phase_queue_to_bitmap(p, st);  // own new frontier -> bitmap[0] (all-zero while top-down runs)
-        grid.sync();
-        push_frontier_slice(p, gcur ^ 1);
-        cross_exchange(p, ++epoch, ++nth, st.level, sums, incoming, &failed);
-        trace_mark(p.s.ctl, ntrace, st.level, 3);
-        gcur ^= 1;
-        if (failed) st.done = 1;
+        switched = true;
+        if (pushed) {
+          gcur ^= 1;  // the new frontier of every rank arrived with exchange #2
+        } else {
+          phase_queue_to_bitmap(p, st);  // own new frontier -> bitmap[0] (all-zero while top-down runs)
+          grid.sync();
+          push_frontier_slice(p, gcur ^ 1);
+          cross_exchange(p, ++epoch, ++nth, st.level, sums, incoming, &failed);
+          trace_mark(p.s.ctl, ntrace, st.level, 3);
+          gcur ^= 1;
+          if (failed) st.done = 1;
+        }
       }
     } else if (nf < (unsigned long long)p.g.n_global / (unsigned)p.tn.beta && nf < st.prev_nf) {
       st.mode = 0;
@@ -1148,12 +1231,17 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_multi_k
       st.cur_q = ld_volatile(&cs->q_count);
       st.cur_wide = ld_volatile(&cs->wide_count);
     }
+    if (pushed && !switched && !st.done) {  // stayed top-down after all: take the frontier bits back
+      phase_unmark(p, st);
+      grid.sync();
+    }
     st.prev_nf = nf;
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     p.s.ctl->result.levels = st.level;
     p.s.ctl->result.td_levels = st.td_levels;
     p.s.ctl->result.bu_levels = st.bu_levels;
+    p.s.ctl->xepoch = epoch;
   }
 }
 
@@ -1191,14 +1279,13 @@ Status run_fused(const BfsParams& p, int64_t src, int grid, cudaStream_t stream,
   return Status();
 }
 
-Status run_fused_multi(const BfsParams& p, int64_t src, unsigned long long epoch_base, int grid, cudaStream_t stream,
-                       int64_t* launches) {
+Status run_fused_multi(const BfsParams& p, int64_t src, int grid, cudaStream_t stream, int64_t* launches) {
   BfsParams pp = p;
   int64_t s = src;
-  unsigned long long e = epoch_base;
-  void* args[] = {&pp, &s, &e};
-  // arrival / release counters of the in-kernel exchanges start from zero in every search
-  B2_CUDA(cudaMemsetAsync(&p.s.ctl->xarrive, 0, 128 + sizeof(unsigned long long), stream));
+  void* args[] = {&pp, &s};
+  // the arrival counter of the in-kernel exchanges starts from zero in every search
+  B2_CUDA(cudaMemsetAsync(&p.s.ctl->xarrive, 0, sizeof(unsigned long long), stream));
+  B2_CUDA(cudaMemsetAsync(&p.s.ctl->xrelease, 0, sizeof(unsigned long long), stream));
   B2_CUDA(cudaLaunchCooperativeKernel((const void*)bfs_fused_multi_kernel, dim3(grid), dim3(kBlock), args, 0, stream));
   if (launches) *launches += 1;
   return Status();
@@ -1226,7 +1313,8 @@ Status run_stepwise(const BfsParams& p, int64_t src, int grid, cudaStream_t stre
     if (trace)
       fprintf(stderr, "[b2bfs] level %d %s frontier q=%u wide=%u unexplored=%llu\n", st.level,
               st.mode ? "bottom-up" : "top-down", st.cur_q, st.cur_wide, st.unexplored);
-    if (st.mode == 0) top_down_kernel<<<grid, kBlock, 0, stream>>>(p, st);
+    const bool claim = claim_only_level(st, p.tn);
+    if (st.mode == 0) top_down_kernel<<<grid, kBlock, 0, stream>>>(p, st, claim);
     else bottom_up_kernel<<<grid, kBlock, 0, stream>>>(p, st);
     ++nl;
     B2_CUDA(cudaMemcpyAsync(pinned, p.s.ctl, sizeof(Control), cudaMemcpyDeviceToHost, stream));
@@ -1235,10 +1323,12 @@ Status run_stepwise(const BfsParams& p, int64_t src, int grid, cudaStream_t stre
     if (trace)
       fprintf(stderr, "[b2bfs]   found q=%u wide=%u bu=%llu edges=%llu\n", ns.q_count, ns.wide_count, ns.bu_count,
               ns.edges);
-    const Conversion cv = advance(st, p.tn, p.g.n, ns.q_count, ns.wide_count, ns.bu_count, ns.edges);
+    const Conversion cv = advance(st, p.tn, p.g.n, ns.q_count, ns.wide_count, ns.bu_count, ns.edges, claim);
     if (cv == kQueueToBitmap) {
-      queue_to_bitmap_kernel<<<grid, kBlock, 0, stream>>>(p, st);
-      ++nl;
+      if (!claim) {  // a claim-only level has left the new frontier in bitmap[0] itself
+        queue_to_bitmap_kernel<<<grid, kBlock, 0, stream>>>(p, st);
+        ++nl;
+      }
     } else if (cv == kBitmapToQueue) {
       bitmap_to_queue_kernel<<<grid, kBlock, 0, stream>>>(p, st);
       ++nl;

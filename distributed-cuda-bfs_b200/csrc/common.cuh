@@ -91,6 +91,7 @@ struct LoopState {
   unsigned int cur_q, cur_wide;
   unsigned long long prev_nf;
   unsigned long long unexplored;  // directed entries whose source is still unvisited
+  unsigned long long frontier_edges;  // degree sum of the current frontier (what this level will scan top-down)
   int td_levels, bu_levels;
 };
 
@@ -109,8 +110,9 @@ struct Control {
   alignas(128) LoopState resume_state;                   // what the group decided, for the CTAs that waited
   int resume_conversion;
   int error;                                             // peer-memory engine: a cross-GPU wait timed out
-  alignas(128) unsigned long long xarrive;               // peer-memory engine: CTAs arrived at exchanges so far
-  alignas(128) unsigned long long xrelease;              // ... and the last exchange CTA 0 has completed
+  alignas(128) unsigned long long xarrive;               // peer-memory engine: CTAs arrived at exchanges so far (this launch)
+  alignas(128) unsigned long long xepoch;                // ... exchanges completed by all searches on this graph so far
+  alignas(128) unsigned long long xrelease;              // exchange variant 1: last exchange the polling CTA has completed
   unsigned int group_exit_seq;                           // bumped when the group leaves its level loop
   int trace_len;                                         // fused engine: per-phase timestamps of CTA 0
   TraceRec trace[kTraceCap];
@@ -152,15 +154,32 @@ struct Tuning {
   int mode;                  // B2BFS_MODE_*
   int alpha;                 // top-down -> bottom-up when m_f > m_u / alpha
   int beta;                  // bottom-up -> top-down when n_f < n / beta
+  int gamma;                 // claim-only top-down level + forced switch when m_f * gamma > m_u / alpha (0: never)
+  int xvariant;              // peer-memory exchange: 0 every CTA polls the record table, 1 one CTA polls and releases the rest
 };
 
 enum Conversion { kNoConversion = 0, kQueueToBitmap = 1, kBitmapToQueue = 2 };
 
+// A top-down level (before the first bottom-up level) whose frontier is already so heavy that the NEXT
+// level is all but certain to run bottom-up does not build the next level's work lists at all: it
+// only claims (visited bit, depth, parent) and leaves the frontier bit of every discovery in
+// bitmap[0]; the switch to bottom-up is then forced.  Skipped per discovery: the row-extent read, the
+// staging and the queue writes.  A wrong guess costs one bottom-up level the heuristic would have
+// run top-down, never a wrong depth.
+__host__ __device__ inline bool claim_only_level(const LoopState& st, const Tuning& tn) {
+  return st.mode == 0 && tn.mode == B2BFS_MODE_DIRECTION_OPT && tn.gamma > 0 && st.level >= 1 && st.bu_levels == 0 &&
+         st.frontier_edges * (unsigned long long)tn.gamma > st.unexplored / (unsigned)tn.alpha;
+}
+
+// `claimed`: the level that just ended was a claim-only one (nbu = its claims, nq/nwide/mf unused).
 __host__ __device__ inline Conversion advance(LoopState& st, const Tuning& tn, int64_t n, unsigned int nq,
-                                              unsigned int nwide, unsigned long long nbu, unsigned long long mf) {
-  const unsigned long long nf = (st.mode == 0) ? (unsigned long long)nq + nwide : nbu;
+                                              unsigned int nwide, unsigned long long nbu, unsigned long long mf,
+                                              bool claimed = false) {
+  const unsigned long long nf = (st.mode == 0 && !claimed) ? (unsigned long long)nq + nwide : nbu;
   if (st.mode == 0) st.td_levels++; else st.bu_levels++;
+  if (claimed) mf = 0;  // degrees of the discoveries were not read
   st.unexplored = (mf > st.unexplored) ? 0ull : st.unexplored - mf;
+  st.frontier_edges = mf;
   st.level++;
   Conversion cv = kNoConversion;
   if (nf == 0) {
@@ -168,10 +187,10 @@ __host__ __device__ inline Conversion advance(LoopState& st, const Tuning& tn, i
   } else if (st.mode == 0) {
     st.cur_q = nq;
     st.cur_wide = nwide;
-    if (tn.mode == B2BFS_MODE_DIRECTION_OPT && mf > st.unexplored / (unsigned)tn.alpha && nf >= st.prev_nf) {
+    if (claimed || (tn.mode == B2BFS_MODE_DIRECTION_OPT && mf > st.unexplored / (unsigned)tn.alpha && nf >= st.prev_nf)) {
       st.mode = 1;
       st.fb = 0;
-      cv = kQueueToBitmap;
+      cv = kQueueToBitmap;  // a claim-only (or marking) level has already left the bits in bitmap[0]
     }
   } else {
     if (nf < (unsigned long long)n / (unsigned)tn.beta && nf < st.prev_nf) {

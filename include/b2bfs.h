@@ -157,6 +157,17 @@ int b2bfs_copy_csr(b2bfs_t* h, int64_t* rowptr_out, int32_t* col_out);
  * b2bfs_copy_csr returns this rank's rows. */
 int b2bfs_run(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent_out, b2bfs_stats* stats);
 
+/* Multi-rank, for callers that are one process per GPU anyway: the same collective search, but every
+ * rank receives only ITS OWN rows - depth_slice_out / parent_slice_out (nullable) hold `count`
+ * entries for vertices [first_vertex, first_vertex + count) as b2bfs_local_range reports them - copied
+ * over that GPU's own PCIe link, with no cross-GPU gather.  Ranks that point their slices into one
+ * shared page-locked segment (b2bfs_host_register on a POSIX shared-memory mapping) assemble the
+ * whole array with all links in parallel.  On a single-GPU handle it is b2bfs_run.
+ * Replaces the rank-1 -> rank-0 MPI_Send of the full distance array and the host min-merge,
+ * bfs_mpi.cu:424-448 (every rank there holds, sends and merges all n entries). */
+int b2bfs_run_slice(b2bfs_t* h, int64_t src, int32_t* depth_slice_out, int32_t* parent_slice_out, b2bfs_stats* stats);
+int b2bfs_local_range(const b2bfs_t* h, int64_t* first_vertex, int64_t* count);
+
 /* Same search, results left in HBM (no device->host copy). */
 int b2bfs_run_device(b2bfs_t* h, int64_t src, b2bfs_stats* stats);
 /* Device pointers to the last search's results (this rank's rows in a multi-rank job). */
@@ -204,6 +215,10 @@ const char* b2bfs_noalloc_last_error(void);
 /* Page-locked host memory for callers that want the copies in b2bfs_run at full PCIe speed. */
 int b2bfs_host_alloc(void** p, int64_t bytes);
 int b2bfs_host_free(void* p);
+/* Page-lock memory the caller already owns (e.g. a shared-memory mapping several ranks write their
+ * slices into); undo with b2bfs_host_unregister before unmapping it. */
+int b2bfs_host_register(void* p, int64_t bytes);
+int b2bfs_host_unregister(void* p);
 
 /* Release everything the handle owns.  The reference never frees (finalizeCuda is commented out,
  * bfs.cu:362-372). */

@@ -32,6 +32,19 @@ def main():
     h = b2.Bfs(local, rank=rank, world=world, nccl_id=ident[0])
     checked = 0
 
+    def check_slices(g, root, want):
+        """b2bfs_run_slice: every rank receives only its own rows; together they are the whole array."""
+        first, cnt = h.local_range()
+        d = np.full(max(cnt, 1), -5, np.int32)[:cnt]
+        q = np.full(max(cnt, 1), -5, np.int32)[:cnt]
+        h.run_slice(int(root), d, q)
+        pieces = [None] * world
+        dist.all_gather_object(pieces, (first, d, q))
+        depth = np.concatenate([x[1] for x in sorted(pieces, key=lambda x: x[0])])
+        parent = np.concatenate([x[2] for x in sorted(pieces, key=lambda x: x[0])])
+        assert depth.shape[0] == g.n and oracle.check_output(depth, want) == -1
+        assert oracle.validate_tree(g, int(root), depth, parent) == (0, -1)
+
     def check(g, roots):
         nonlocal checked
         for root in roots:
@@ -49,6 +62,8 @@ def main():
                 checked += 1
         h.set_option("mode", b2.MODE_DIRECTION_OPT)
         h.set_option("multi_engine", 0)
+        check_slices(g, roots[0], oracle.bfs_serial(g, int(roots[0])))
+        checked += 1
 
     # synthetic graphs, generated on every rank, each keeping its own rows
     for kind, scale, ef, seed in ((1, 16, 16, 1), (0, 14, 16, 3), (2, 12, 0, 0), (1, 9, 4, 5)):
@@ -62,6 +77,20 @@ def main():
         rng = np.random.default_rng(seed)
         roots = list(rng.choice(np.flatnonzero(g.sizes > 0), 4, replace=False)) + [0, n - 1]
         check(g, roots)
+    # a graph large enough for every level kind (marking top-down, several bottom-up levels, tail levels)
+    # to carry real traffic between the ranks; depths pinned by the edge rules (no host CSR needed)
+    n, s, d = oracle.generate_edges(1, 20, 16, 2)
+    h.generate(1, 20, 16, 2)
+    rdeg = h.row_degrees()
+    for root in np.random.default_rng(7).choice(np.flatnonzero(rdeg > 0), 6, replace=False):
+        for engine in (0, 1):
+            h.set_option("multi_engine", engine)
+            depth, _ = h.run(int(root))
+            bad = oracle.check_depth_by_edges(n, s, d, int(root), depth)
+            assert bad == -1, f"rank {rank} kron-20 root {root} engine {engine}: vertex {bad} depth {depth[bad]}"
+            checked += 1
+    h.set_option("multi_engine", 0)
+    del s, d
     # the reference's golden vectors through the text loader (every rank parses the file, as every
     # MPI rank of the reference does, bfs_mpi.cu:815)
     for name in golden_names():

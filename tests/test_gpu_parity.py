@@ -123,6 +123,22 @@ def test_random_roots_depth_and_parent(b2, gpu, kind, scale, ef, seed, nroots):
         _check_search(b2, gpu, g, int(r))
 
 
+@pytest.mark.parametrize("gamma", [0, 1, 24, 1 << 20])
+@pytest.mark.parametrize("kind,scale,ef,seed", [(0, 16, 16, 1), (1, 15, 16, 5), (2, 12, 0, 0), (0, 13, 2, 4)])
+def test_claim_only_levels_change_no_depth(b2, kind, scale, ef, seed, gamma):
+    """Option "gamma" decides when a top-down level only claims (no work lists for the next level)
+    and forces the switch to bottom-up: gamma = 0 never, 2^20 at the first level >= 1 with any
+    frontier at all.  Depths, tree validity and the reach statistics must not depend on it."""
+    n, s, d = oracle.generate_edges(kind, scale, ef, seed)
+    g = oracle.build_csr(n, s, d)
+    with b2.Bfs(0, gamma=gamma) as h:
+        h.generate(kind, scale, ef, seed)
+        assert h.get_option("gamma") == gamma
+        rng = np.random.default_rng(seed + gamma)
+        for r in rng.choice(np.flatnonzero(g.sizes > 0), 4, replace=False):
+            _check_search(b2, h, g, int(r))
+
+
 def test_hub_rows_and_no_dedup(b2):
     """A star whose centre row is cut into many wide work items, plus duplicates and self-loops kept."""
     n = 20000
