@@ -45,6 +45,12 @@ class Stats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved0"}
 
 
+class BatchStats(C.Structure):
+    _fields_ = [("nroots", C.c_int32), ("levels", C.c_int32), ("kernel_launches", C.c_int64), ("d2h_bytes", C.c_int64),
+                ("search_ms", C.c_double), ("total_ms", C.c_double),
+                ("reached_vertices", C.c_int64 * 64), ("reached_entries", C.c_int64 * 64)]
+
+
 def build(verbose: bool = False) -> None:
     """Compile lib/libb2bfs.so and bin/b2bfs for sm_100a (nvcc cross-compiles without a GPU)."""
     r = subprocess.run(["make", "-C", _HERE, "-j8", "all"], capture_output=True, text=True)
@@ -92,6 +98,8 @@ def lib() -> C.CDLL:
             "b2bfs_local_range": ([vp, C.POINTER(i64), C.POINTER(i64)], C.c_int),
             "b2bfs_host_register": ([vp, i64], C.c_int),
             "b2bfs_host_unregister": ([vp], C.c_int),
+            "b2bfs_run_batch": ([vp, C.c_int, vp, i32p, C.POINTER(BatchStats)], C.c_int),
+            "b2bfs_device_batch_depth": ([vp, C.POINTER(vp)], C.c_int),
             "b2bfs_device_depth": ([vp, C.POINTER(vp)], C.c_int),
             "b2bfs_device_parent": ([vp, C.POINTER(vp)], C.c_int),
             "b2bfs_last_trace": ([vp, vp, vp, vp, C.c_int], C.c_int),
@@ -353,6 +361,21 @@ class Bfs:
         self._check(lib().b2bfs_run_slice(self._h, int(src), depth_slice.ctypes.data,
                                           parent_slice.ctypes.data if parent_slice is not None else None, C.byref(st)))
         return st.as_dict()
+
+    def run_batch(self, roots, depth_out=None, to_host: bool = True):
+        """Up to 64 searches in one pass per level (b2bfs_run_batch).  Returns (depth[len(roots), n] or
+        None, stats dict with per-root reached_vertices / reached_entries lists)."""
+        roots = np.ascontiguousarray(roots, np.int64)
+        k = int(roots.shape[0])
+        depth = None
+        if to_host:
+            depth = depth_out if depth_out is not None else np.empty((k, self.num_vertices), np.int32)
+        st = BatchStats()
+        self._check(lib().b2bfs_run_batch(self._h, k, roots.ctypes.data, depth.ctypes.data if depth is not None else None,
+                                          C.byref(st)))
+        return depth, {"nroots": st.nroots, "levels": st.levels, "kernel_launches": st.kernel_launches,
+                       "d2h_bytes": st.d2h_bytes, "search_ms": st.search_ms, "total_ms": st.total_ms,
+                       "reached_vertices": list(st.reached_vertices[:k]), "reached_entries": list(st.reached_entries[:k])}
 
     def run_device(self, src: int):
         st = Stats()

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "../../include/b2bfs_graphgen.h"
+#include "batch.cuh"
 #include "bfs.cuh"
 #include "build.cuh"
 #include "edge_file.hpp"
@@ -25,13 +26,14 @@ struct b2bfs {
   std::string err;
   // options
   int dedup = 1, mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED;
-  int alpha = 14, beta = 24, gamma = 24, xvariant = 0, keep_edges = 1, gather_parent = 1, hub_first = 1;
+  int alpha = 14, beta = 24, gamma = 400, xvariant = 0, keep_edges = 1, gather_parent = 1, hub_first = 1, directed = 0;
   // graph
   bool has_graph = false;
   int64_t n = 0, m = 0;
   int32_t *d_src = nullptr, *d_dst = nullptr;
   BuiltCsr csr;
   // search state
+  BatchState batch;  // allocated by the first b2bfs_run_batch on this graph
   SearchView sv{};
   Control* pinned_ctl = nullptr;
   int grid = 0;
@@ -110,6 +112,7 @@ static void free_multi_state(b2bfs* h) {
 
 static void free_graph(b2bfs* h) {
   free_multi_state(h);
+  free_batch(&h->batch);
   cudaFree(h->d_src);
   cudaFree(h->d_dst);
   h->d_src = h->d_dst = nullptr;
@@ -140,7 +143,7 @@ static int finish_load(b2bfs* h) {
     h->nloc = h->n;
   }
   Status s = build_csr_device(h->d_src, h->d_dst, h->m, h->n, h->vbase, h->vbase + h->nloc, multi, h->dedup,
-                              h->hub_first, multi ? h->part / 32 : 0, h->stream, &h->csr, &h->build_launches);
+                              h->hub_first, h->directed, multi ? h->part / 32 : 0, h->stream, &h->csr, &h->build_launches);
   if (!s.ok()) {
     free_graph(h);
     return fail(h, s);
@@ -254,7 +257,7 @@ static BfsParams make_params(const b2bfs* h) {
   for (int r = 0; r < 8; ++r) p.s.xbase[r] = p2p ? h->xpeer[r] : nullptr;
   p.g.n_global = h->n;
   p.g.entries_global = multi ? (unsigned long long)h->mc.entries_global : (unsigned long long)h->csr.entries;
-  p.tn.mode = h->mode;
+  p.tn.mode = h->directed ? B2BFS_MODE_TOP_DOWN : h->mode;  // bottom-up needs in-edges = out-edges
   p.tn.alpha = h->alpha;
   p.tn.beta = h->beta;
   p.tn.gamma = h->gamma;
@@ -447,11 +450,15 @@ int b2bfs_create_rank(b2bfs_t** out, int device, int rank, int world, const void
 int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
   if (!h || !key) return fail(h, B2BFS_ERR_ARG, "b2bfs_set_option: null argument");
   const std::string k(key);
-  const bool graph_time = (k == "dedup" || k == "keep_edges" || k == "hub_first");
+  const bool graph_time = (k == "dedup" || k == "keep_edges" || k == "hub_first" || k == "directed");
   if (graph_time && h->has_graph) return fail(h, B2BFS_ERR_STATE, "option '" + k + "' must be set before loading a graph");
   if (k == "dedup" && (value == 0 || value == 1)) h->dedup = (int)value;
   else if (k == "keep_edges" && (value == 0 || value == 1)) h->keep_edges = (int)value;
   else if (k == "hub_first" && (value == 0 || value == 1)) h->hub_first = (int)value;
+  else if (k == "directed" && (value == 0 || value == 1)) {
+    if (value && h->world > 1) return fail(h, B2BFS_ERR_UNSUPPORTED, "directed graphs: single-GPU handles only");
+    h->directed = (int)value;
+  }
   else if (k == "mode" && (value == B2BFS_MODE_DIRECTION_OPT || value == B2BFS_MODE_TOP_DOWN)) h->mode = (int)value;
   else if (k == "engine" && (value == B2BFS_ENGINE_FUSED || value == B2BFS_ENGINE_STEPWISE)) h->engine = (int)value;
   else if (k == "gather_parent" && (value == 0 || value == 1)) h->gather_parent = (int)value;
@@ -470,6 +477,7 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   if (k == "dedup") *value = h->dedup;
   else if (k == "keep_edges") *value = h->keep_edges;
   else if (k == "hub_first") *value = h->hub_first;
+  else if (k == "directed") *value = h->directed;
   else if (k == "mode") *value = h->mode;
   else if (k == "engine") *value = h->engine;
   else if (k == "alpha") *value = h->alpha;
@@ -571,7 +579,7 @@ int b2bfs_num_vertices(const b2bfs_t* h, int64_t* n) {
 }
 int b2bfs_num_edges(const b2bfs_t* h, int64_t* two_m) {
   if (!h || !two_m) return B2BFS_ERR_ARG;
-  *two_m = 2 * h->m;
+  *two_m = h->directed ? h->m : 2 * h->m;  // G.numEdges: adjacency entries (bfs.cu:875; readGraph bfs.cu:919)
   return B2BFS_OK;
 }
 int b2bfs_num_input_edges(const b2bfs_t* h, int64_t* m) {
@@ -742,6 +750,55 @@ int b2bfs_local_range(const b2bfs_t* h, int64_t* first_vertex, int64_t* count) {
   if (!h || !first_vertex || !count || !h->has_graph) return B2BFS_ERR_ARG;
   *first_vertex = h->vbase;
   *count = h->nloc;
+  return B2BFS_OK;
+}
+
+int b2bfs_run_batch(b2bfs_t* h, int nroots, const int64_t* roots, int32_t* depth_out, b2bfs_batch_stats* stats) {
+  if (!h || !roots) return fail(h, B2BFS_ERR_ARG, "b2bfs_run_batch: null argument");
+  if (!h->has_graph) return fail(h, B2BFS_ERR_STATE, "b2bfs_run_batch: no graph resident");
+  if (nroots < 1 || nroots > B2BFS_BATCH_MAX) return fail(h, B2BFS_ERR_ARG, "b2bfs_run_batch: need 1 <= nroots <= 64");
+  if (h->world > 1) return fail(h, B2BFS_ERR_UNSUPPORTED, "b2bfs_run_batch: single-GPU handles only");
+  if (h->directed) return fail(h, B2BFS_ERR_UNSUPPORTED, "b2bfs_run_batch pulls over in-edges: not available for a directed graph");
+  for (int i = 0; i < nroots; ++i)
+    if (roots[i] < 0 || roots[i] >= h->n) return fail(h, B2BFS_ERR_ARG, "b2bfs_run_batch: source vertex outside [0, vertex_num)");
+  const auto t0 = std::chrono::steady_clock::now();
+  API_CUDA(h, cudaSetDevice(h->device));
+  int64_t launches = 0;
+  Status s = prepare_batch(&h->batch, h->n, h->csr.wide_items, h->csr.rowptr, nroots, h->stream, &launches);
+  if (!s.ok()) { free_batch(&h->batch); return fail(h, s); }
+  int levels = 0;
+  s = run_batch(&h->batch, h->n, h->csr.rowptr, h->csr.col, nroots, roots, h->grid, h->stream, h->ev0, h->ev1, &levels, &launches);
+  if (!s.ok()) return fail(h, s);
+  int64_t d2h = 0;
+  if (depth_out) {
+    API_CUDA(h, cudaMemcpyAsync(depth_out, h->batch.depth, (size_t)nroots * (size_t)h->n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    d2h += (int64_t)nroots * h->n * (int64_t)sizeof(int32_t);
+  }
+  API_CUDA(h, cudaStreamSynchronize(h->stream));
+  if (stats) {
+    unsigned long long vd[128];
+    s = batch_reach_stats(&h->batch, h->n, h->csr.orig_deg, h->stream, vd, &launches);
+    if (!s.ok()) return fail(h, s);
+    float ms = 0.f;
+    API_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+    memset(stats, 0, sizeof(*stats));
+    stats->nroots = nroots;
+    stats->levels = levels;
+    stats->kernel_launches = launches;
+    stats->d2h_bytes = d2h;
+    stats->search_ms = ms;
+    for (int i = 0; i < nroots; ++i) {
+      stats->reached_vertices[i] = (int64_t)vd[i];
+      stats->reached_entries[i] = (int64_t)vd[64 + i];
+    }
+    stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  }
+  return B2BFS_OK;
+}
+
+int b2bfs_device_batch_depth(const b2bfs_t* h, const int32_t** depth_dev) {
+  if (!h || !depth_dev || !h->batch.depth) return B2BFS_ERR_ARG;
+  *depth_dev = h->batch.depth;
   return B2BFS_OK;
 }
 

@@ -23,7 +23,8 @@ Status generate_edges_device(int kind, int scale, int ef, uint64_t seed, int64_t
                              int32_t* dst, cudaStream_t stream);
 
 Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64_t n, int64_t row_begin,
-                        int64_t row_end, bool partitioned, int dedup, int hub_first, int64_t nwords_override,
+                        int64_t row_end, bool partitioned, int dedup, int hub_first, int directed,
+                        int64_t nwords_override,
                         cudaStream_t stream,
                         BuiltCsr* out, int64_t* launches);
 

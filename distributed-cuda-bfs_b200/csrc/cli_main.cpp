@@ -8,6 +8,14 @@
 // binary then self-checks the depth array against a serial host BFS over the same tuples; that
 // check is verification only (skip it with --no-check) — there is no CPU fallback.
 //
+// The reference's second reader, readGraph (bfs.cu:882-920; dead code in its main), is here too:
+//   b2bfs <src_vertex> --stdin            "n m" + m pairs from standard input, every pair the single
+//                                         arc u -> v (bfs.cu:899-901: NOT symmetrised; searched top-down)
+//   b2bfs <src_vertex> --random N M       srand(12345); u = rand() % N; v = rand() % N per edge, both
+//                                         directions (bfs.cu:891-906) - the C library's own rand() stream
+// (`b2bfs <src_vertex>` alone and `b2bfs <src_vertex> N M` are accepted as the same two forms, which
+// is how readGraph itself reads its argv: argc <= 2 means stdin, else argv[2] = n and argv[3] = m.)
+//
 // Extra, optional flags after the two positionals:
 //   --no-check            skip the host self-check
 //   --dump-depth PATH     write one decimal depth per line (2147483647 = unreachable)
@@ -37,13 +45,13 @@ static int die(b2bfs_t* h, const char* what, int rc) {
 
 // serial host BFS for the self-check: same role as bfsCPU (bfs.cu:923-945), written for this file
 static void host_check_bfs(int64_t n, int64_t m, const std::vector<int32_t>& s, const std::vector<int32_t>& d,
-                           int64_t start, std::vector<int32_t>& depth) {
+                           int64_t start, std::vector<int32_t>& depth, bool directed) {
   std::vector<int64_t> off(n + 1, 0);
-  for (int64_t i = 0; i < m; ++i) { off[s[i] + 1]++; off[d[i] + 1]++; }
+  for (int64_t i = 0; i < m; ++i) { off[s[i] + 1]++; if (!directed) off[d[i] + 1]++; }
   for (int64_t v = 0; v < n; ++v) off[v + 1] += off[v];
-  std::vector<int32_t> adj(2 * m);
+  std::vector<int32_t> adj(directed ? m : 2 * m);
   std::vector<int64_t> cur(off.begin(), off.end() - 1);
-  for (int64_t i = 0; i < m; ++i) { adj[cur[s[i]]++] = d[i]; adj[cur[d[i]]++] = s[i]; }
+  for (int64_t i = 0; i < m; ++i) { adj[cur[s[i]]++] = d[i]; if (!directed) adj[cur[d[i]]++] = s[i]; }
   depth.assign(n, INT_MAX);
   std::vector<int32_t> q;
   q.reserve(n);
@@ -58,21 +66,47 @@ static void host_check_bfs(int64_t n, int64_t m, const std::vector<int32_t>& s, 
   }
 }
 
+static bool all_digits(const char* s) {
+  if (!*s) return false;
+  for (; *s; ++s) if (*s < '0' || *s > '9') return false;
+  return true;
+}
+
 int main(int argc, char** argv) {
-  if (argc < 3) {
-    fprintf(stderr, "usage: %s <src_vertex> <edge_file> [--no-check] [--dump-depth PATH] [--mode do|td] "
-                    "[--engine fused|stepwise] [--no-dedup] [--gen KIND:SCALE:EF:SEED] [--device N]\n", argv[0]);
+  if (argc < 2) {
+    fprintf(stderr, "usage: %s <src_vertex> <edge_file> | <src_vertex> --stdin | <src_vertex> --random N M\n"
+                    "       [--no-check] [--dump-depth PATH] [--mode do|td] [--engine fused|stepwise] [--no-dedup] "
+                    "[--gen KIND:SCALE:EF:SEED] [--format auto|ref|mtx|snap|bin] [--save-cache PATH] [--device N]\n", argv[0]);
     return 2;
   }
   const int64_t start = atoll(argv[1]);  // bfs.cu:786
-  const char* path = argv[2];
+  // which reader: readGraphFromFile (the reference's live one) or one of readGraph's two forms
+  enum { kFile, kStdin, kRandom } source = kFile;
+  long long rand_n = 0, rand_m = 0;
+  int first_flag = 3;
+  const char* path = argc > 2 ? argv[2] : "(stdin)";
+  if (argc == 2 || !strcmp(argv[2], "--stdin")) {
+    source = kStdin;
+    path = "(stdin)";
+    first_flag = argc == 2 ? 2 : 3;
+  } else if (!strcmp(argv[2], "--random") && argc >= 5) {
+    source = kRandom;
+    rand_n = atoll(argv[3]);
+    rand_m = atoll(argv[4]);
+    first_flag = 5;
+  } else if (argc >= 4 && all_digits(argv[2]) && all_digits(argv[3])) {  // readGraph's own argv layout
+    source = kRandom;
+    rand_n = atoll(argv[2]);
+    rand_m = atoll(argv[3]);
+    first_flag = 4;
+  }
   bool check = true, dedup = true;
   const char* dump = nullptr;
   const char* gen = nullptr;
   const char* save_cache = nullptr;
   int format = B2BFS_FORMAT_REFERENCE;
   int mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED, device = 0;
-  for (int i = 3; i < argc; ++i) {
+  for (int i = first_flag; i < argc; ++i) {
     const std::string a(argv[i]);
     if (a == "--no-check") check = false;
     else if (a == "--no-dedup") dedup = false;
@@ -97,8 +131,34 @@ int main(int argc, char** argv) {
   b2bfs_set_option(h, "mode", mode);
   b2bfs_set_option(h, "engine", engine);
 
-  printf("%s\n", path);  // bfs.cu:830
-  if (gen) {
+  if (source == kFile) printf("%s\n", path);  // bfs.cu:830
+  if (source == kStdin || source == kRandom) {
+    long long n = rand_n, m = rand_m;
+    std::vector<int32_t> s, d;
+    if (source == kStdin) {
+      if (scanf("%lld %lld", &n, &m) != 2 || n < 1 || m < 0) { fprintf(stderr, "b2bfs: stdin must start with \"n m\"\n"); return 2; }
+      s.resize((size_t)m);
+      d.resize((size_t)m);
+      for (long long i = 0; i < m; ++i) {
+        int u, v;
+        if (scanf("%d %d", &u, &v) != 2) { fprintf(stderr, "b2bfs: stdin ends after %lld of %lld pairs\n", i, m); return 2; }
+        s[(size_t)i] = u;
+        d[(size_t)i] = v;
+      }
+      b2bfs_set_option(h, "directed", 1);  // bfs.cu:901 pushes v onto u's list only
+    } else {
+      if (n < 1 || n > INT_MAX || m < 0) { fprintf(stderr, "b2bfs: --random needs N >= 1 and M >= 0\n"); return 2; }
+      s.resize((size_t)m);
+      d.resize((size_t)m);
+      srand(12345);  // bfs.cu:892
+      for (long long i = 0; i < m; ++i) {
+        s[(size_t)i] = (int32_t)(rand() % n);  // bfs.cu:903
+        d[(size_t)i] = (int32_t)(rand() % n);  // bfs.cu:904
+      }
+    }
+    rc = b2bfs_load_edges(h, n, m, s.data(), d.data());
+    if (rc) return die(h, "b2bfs_load_edges", rc);
+  } else if (gen) {
     char kind[16] = {0};
     int scale = 0, ef = 16;
     unsigned long long seed = 1;
@@ -121,9 +181,11 @@ int main(int argc, char** argv) {
   b2bfs_num_vertices(h, &n);
   b2bfs_num_input_edges(h, &m);
   b2bfs_num_edges(h, &e2);
-  printf("nodes num: %lld\n", (long long)n);  // bfs.cu:846
-  printf("edge num: %lld\n", (long long)m);   // bfs.cu:848
-  printf("finish load graph\n");              // bfs.cu:876
+  if (source == kFile) {  // readGraph prints nothing of its own
+    printf("nodes num: %lld\n", (long long)n);  // bfs.cu:846
+    printf("edge num: %lld\n", (long long)m);   // bfs.cu:848
+    printf("finish load graph\n");              // bfs.cu:876
+  }
   printf("Number of vertices %lld\n", (long long)n);    // bfs.cu:789
   printf("Number of edges %lld\n\n", (long long)e2);    // bfs.cu:790
   if (start < 0 || start >= n) {
@@ -139,7 +201,7 @@ int main(int argc, char** argv) {
     if (rc) return die(h, "b2bfs_copy_edges", rc);
     printf("Starting sequential bfs.\n");  // bfs.cu:213
     const auto t0 = std::chrono::steady_clock::now();
-    host_check_bfs(n, m, s, d, start, expected);
+    host_check_bfs(n, m, s, d, start, expected, source == kStdin);
     const long ms = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
     printf("Elapsed time in milliseconds : %li ms.\n\n", ms);  // bfs.cu:218
   }

@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(kBlock) expand_edges_kernel(const int32_t* __r
                                                               int vbits, int rshift, const uint32_t* __restrict__ degc,
                                                               int64_t row_begin, int64_t row_end,
                                                               uint64_t* __restrict__ keys,
-                                                              unsigned long long* cursor, int* bad_flag) {
+                                                              unsigned long long* cursor, int* bad_flag, int directed) {
   const int lane = threadIdx.x & 31;
   const int64_t stride = (int64_t)gridDim.x * kBlock;
   const int64_t rounds = (m + stride - 1) / stride;
@@ -69,7 +69,10 @@ __global__ void __launch_bounds__(kBlock) expand_edges_kernel(const int32_t* __r
       cu = (uint64_t)(15 - min(15, 31 - __clz((int)max(degc[u], 1u)))) << vbits;
       cv = (uint64_t)(15 - min(15, 31 - __clz((int)max(degc[v], 1u)))) << vbits;
     }
-    if (cursor == nullptr) {
+    if (directed) {  // the reference's stdin reader: one arc per tuple (bfs.cu:901)
+      if (ok) keys[i] = ((uint64_t)u << rshift) | cv | (uint64_t)v;
+      else if (i < m) keys[i] = 0;
+    } else if (cursor == nullptr) {
       if (ok) {
         keys[2 * i] = ((uint64_t)u << rshift) | cv | (uint64_t)v;
         keys[2 * i + 1] = ((uint64_t)v << rshift) | cu | (uint64_t)u;
@@ -203,7 +206,7 @@ __global__ void __launch_bounds__(kBlock) finish_rows_kernel(int64_t nrows, int6
                                                              uint32_t* __restrict__ visited_init,
                                                              int32_t* __restrict__ first_nbr,
                                                              unsigned long long* wide_items,
-                                                             unsigned long long* max_degree) {
+                                                             unsigned long long* max_degree, int directed) {
   const int lane = threadIdx.x & 31;
   const int64_t warps = (int64_t)gridDim.x * kWarpsPerBlock;
   unsigned long long mx = 0;
@@ -216,7 +219,7 @@ __global__ void __launch_bounds__(kBlock) finish_rows_kernel(int64_t nrows, int6
       const int64_t d = rowptr[v + 1] - rowptr[v];
       first_nbr[v] = d > 0 ? col[rowptr[v]] : -1;
       orig_deg[v] = (uint32_t)(orig_rowptr[v + 1] - orig_rowptr[v]);
-      skip = d == 0;
+      skip = d == 0 && !directed;  // a vertex without out-arcs can still be reached over an in-arc
       if (d >= kNarrow) items = (unsigned long long)((d + kChunk - 1) / kChunk);
       mx = d > (int64_t)mx ? (unsigned long long)d : mx;
     }
@@ -253,14 +256,15 @@ static int bits_for(int64_t n) {
 }
 
 Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64_t n, int64_t row_begin,
-                        int64_t row_end, bool partitioned, int dedup, int hub_first, int64_t nwords_override,
-                        cudaStream_t stream,
+                        int64_t row_end, bool partitioned, int dedup, int hub_first, int directed,
+                        int64_t nwords_override, cudaStream_t stream,
                         BuiltCsr* out, int64_t* launches) {
   *out = BuiltCsr();
   const int64_t nrows = row_end - row_begin;
   const int vbits = bits_for(n);
   const int rbits = bits_for(nrows > 0 ? nrows : 1);
-  const int cbits = (hub_first && vbits + rbits + 4 <= 64) ? 4 : 0;
+  if (directed && partitioned) return make_error(B2BFS_ERR_UNSUPPORTED, "directed graphs are not partitioned across GPUs");
+  const int cbits = (hub_first && !directed && vbits + rbits + 4 <= 64) ? 4 : 0;
   const int rshift = vbits + cbits;
   const int64_t nwords = nwords_override > 0 ? nwords_override : ((nrows + 31) / 32 + 3) / 4 * 4;
   out->nrows = nrows;
@@ -276,7 +280,7 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
 
   const int64_t eblocks = (m + kBlock - 1) / kBlock;
   const int egrid = (int)(eblocks < (int64_t)kSMs * 16 ? (eblocks > 0 ? eblocks : 1) : (int64_t)kSMs * 16);
-  int64_t N = 2 * m;
+  int64_t N = directed ? m : 2 * m;
   if (partitioned) {
     count_owned_kernel<<<egrid, kBlock, 0, stream>>>(src, dst, m, row_begin, row_end, counters);
     unsigned long long owned = 0;
@@ -303,7 +307,7 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
     if (launches) *launches += 1;
   }
   expand_edges_kernel<<<egrid, kBlock, 0, stream>>>(src, dst, m, n, vbits, rshift, degc, row_begin, row_end, ka,
-                                                    partitioned ? counters : nullptr, bad);
+                                                    partitioned ? counters : nullptr, bad, directed);
   if (launches) *launches += 1;
   int bad_h = 0;
   B2_CUDA(cudaMemcpyAsync(&bad_h, bad, sizeof(int), cudaMemcpyDeviceToHost, stream));
@@ -350,7 +354,7 @@ Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64
   const int64_t fblocks = (nwords + kWarpsPerBlock - 1) / kWarpsPerBlock;
   const int fgrid = (int)(fblocks < (int64_t)kSMs * 8 ? fblocks : (int64_t)kSMs * 8);
   finish_rows_kernel<<<fgrid, kBlock, 0, stream>>>(nrows, nwords, out->rowptr, orig_rowptr, out->orig_deg, out->col,
-                                                   out->visited_init, out->first_nbr, counters + 1, counters + 2);
+                                                   out->visited_init, out->first_nbr, counters + 1, counters + 2, directed);
   if (launches) *launches += 1;
   unsigned long long hc[2] = {0, 0};
   B2_CUDA(cudaMemcpyAsync(hc, counters + 1, sizeof(hc), cudaMemcpyDeviceToHost, stream));

@@ -85,7 +85,11 @@ int b2bfs_comm_unique_id(void* out128);
  * floor(log2 degree), then ascending id, so that bottom-up meets a hub first; 0: ascending id),
  * "multi_engine" (multi-rank: 0 peer-memory kernel, 1 NCCL per level), "mode", "engine" (these
  * three may change between searches), "alpha", "beta" (switch
- * heuristic), "keep_edges" (1: keep the input tuples resident for b2bfs_copy_edges).
+ * heuristic), "gamma" (a top-down level whose frontier degree sum times gamma exceeds the
+ * unexplored entries / alpha only claims vertices and forces the switch to bottom-up; 0 = never),
+ * "keep_edges" (1: keep the input tuples resident for b2bfs_copy_edges), "directed" (1: a tuple
+ * "u v" is the single arc u -> v, as the reference's stdin reader builds it, bfs.cu:901, instead of
+ * an undirected edge, bfs.cu:860-861; such graphs are searched top-down only, on one GPU).
  * Replaces the reference's compile-time switches (#define DeviceNum, commented call sites in main,
  * bfs.cu:19, 805-819). */
 int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value);
@@ -167,6 +171,27 @@ int b2bfs_run(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent_out, 
  * bfs_mpi.cu:424-448 (every rank there holds, sends and merges all n entries). */
 int b2bfs_run_slice(b2bfs_t* h, int64_t src, int32_t* depth_slice_out, int32_t* parent_slice_out, b2bfs_stats* stats);
 int b2bfs_local_range(const b2bfs_t* h, int64_t* first_vertex, int64_t* count);
+
+/* Up to 64 searches over the resident graph in one pass per level (the reference
+ * has no batched search - its metric's 64 roots would be 64 runs of runCudaQueueBfs, bfs.cu:542).
+ * Bit-parallel multi-source BFS: one 64-bit word per vertex and role, one read of the adjacency
+ * serves every search of the batch.  depth_out (nullable): nroots x n int32, row i = the depth array
+ * b2bfs_run would return for roots[i] (INT_MAX = unreachable).  Depths only: no parent tree.
+ * Single-GPU handles, undirected graphs.  The first call on a graph allocates 24 bytes per vertex
+ * of state plus 4*n bytes per root. */
+#define B2BFS_BATCH_MAX 64
+typedef struct b2bfs_batch_stats {
+  int32_t nroots;
+  int32_t levels;              /* levels executed = largest eccentricity in the batch + 1 */
+  int64_t kernel_launches;
+  int64_t d2h_bytes;
+  double search_ms;            /* device time, CUDA events: state reset .. all depth rows complete in HBM */
+  double total_ms;
+  int64_t reached_vertices[B2BFS_BATCH_MAX]; /* V_r per root */
+  int64_t reached_entries[B2BFS_BATCH_MAX];  /* D_r per root */
+} b2bfs_batch_stats;
+int b2bfs_run_batch(b2bfs_t* h, int nroots, const int64_t* roots, int32_t* depth_out, b2bfs_batch_stats* stats);
+int b2bfs_device_batch_depth(const b2bfs_t* h, const int32_t** depth_dev);
 
 /* Same search, results left in HBM (no device->host copy). */
 int b2bfs_run_device(b2bfs_t* h, int64_t src, b2bfs_stats* stats);

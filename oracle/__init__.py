@@ -71,6 +71,10 @@ def lib() -> C.CDLL:
         L.oracle_bfs_parallel.argtypes = [C.c_int64, _i64p, _i32p, _i32p, C.c_int64, _i32p, C.c_int]
         L.oracle_bfs_parallel.restype = C.c_int64
         L.oracle_num_threads.restype = C.c_int
+        L.oracle_build_csr_directed.argtypes = [C.c_int64, C.c_int64, _i32p, _i32p, _i64p, _i32p, _i32p]
+        L.oracle_build_csr_directed.restype = C.c_int
+        L.oracle_random_edges.argtypes = [C.c_int64, C.c_int64, _i32p, _i32p]
+        L.oracle_random_edges.restype = None
         L.oracle_build_csr_parallel.argtypes = [C.c_int64, C.c_int64, _i32p, _i32p, _i64p, _i32p, _i32p, C.c_int]
         L.oracle_build_csr_parallel.restype = C.c_int
         L.oracle_check_depth_by_edges.argtypes = [C.c_int64, C.c_int64, _i32p, _i32p, C.c_int64, _i32p, C.c_int]
@@ -102,6 +106,10 @@ def ref() -> C.CDLL:
         R.ref_num_edges.restype = C.c_int
         R.ref_get_csr.argtypes = [_i32p, _i32p, _i32p]
         R.ref_get_csr.restype = None
+        R.ref_read_graph_stdin.argtypes = [C.c_char_p]
+        R.ref_read_graph_stdin.restype = C.c_int
+        R.ref_read_graph_random.argtypes = [C.c_int, C.c_int]
+        R.ref_read_graph_random.restype = C.c_int
         R.ref_bfs_cpu.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
         R.ref_bfs_cpu.restype = C.c_int64
         _ref = R
@@ -152,6 +160,28 @@ def build_csr(n: int, src, dst) -> Csr:
     if rc:
         raise ValueError(f"oracle_build_csr -> {rc}")
     return Csr(n, offsets, sizes, adj)
+
+
+def build_csr_directed(n: int, src, dst) -> Csr:
+    """The reference's stdin reader (readGraph, bfs.cu:882-920): every tuple is the single arc u -> v."""
+    src = np.ascontiguousarray(src, np.int32)
+    dst = np.ascontiguousarray(dst, np.int32)
+    m = src.shape[0]
+    offsets = np.empty(max(n, 1), np.int64)[:n]
+    sizes = np.empty(max(n, 1), np.int32)[:n]
+    adj = np.empty(max(m, 1), np.int32)[:m]
+    rc = lib().oracle_build_csr_directed(n, m, src, dst, offsets, sizes, adj)
+    if rc:
+        raise ValueError(f"oracle_build_csr_directed -> {rc}")
+    return Csr(n, offsets, sizes, adj)
+
+
+def random_edges(n: int, m: int):
+    """The tuples of the reference's random-graph reader: srand(12345), rand() % n twice per edge."""
+    src = np.empty(m, np.int32)
+    dst = np.empty(m, np.int32)
+    lib().oracle_random_edges(n, m, src, dst)
+    return src, dst
 
 
 def build_csr_parallel(n: int, src, dst, threads: int = 0) -> Csr:
@@ -270,6 +300,28 @@ def ref_load_file(path: str) -> Csr:
     adj = np.empty(e, np.int32)
     R.ref_get_csr(offsets, sizes, adj)
     return Csr(n, offsets.astype(np.int64), sizes, adj)
+
+
+def _ref_current_graph() -> Csr:
+    R = ref()
+    n, e = R.ref_num_vertices(), R.ref_num_edges()
+    offsets = np.empty(n, np.int32)
+    sizes = np.empty(n, np.int32)
+    adj = np.empty(max(e, 1), np.int32)[:e]
+    R.ref_get_csr(offsets, sizes, adj)
+    return Csr(n, offsets.astype(np.int64), sizes, adj)
+
+
+def ref_read_graph_stdin(path: str) -> Csr:
+    """The reference's readGraph in its stdin form, fed from `path` (bfs.cu:882-920)."""
+    ref().ref_read_graph_stdin(path.encode())
+    return _ref_current_graph()
+
+
+def ref_read_graph_random(n: int, m: int) -> Csr:
+    """The reference's readGraph in its random form: srand(12345), n = argv[2], m = argv[3]."""
+    ref().ref_read_graph_random(n, m)
+    return _ref_current_graph()
 
 
 def ref_set_graph(g: Csr) -> None:

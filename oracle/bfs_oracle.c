@@ -572,3 +572,37 @@ int64_t oracle_bfs_serial_bounded(int64_t n, const int64_t* offsets, const int32
   if (reached_out) *reached_out = tail;
   return scanned;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * The reference's second reader, readGraph (bfs.cu:882-920; never called by its main).
+ *   stdin form  (bfs.cu:888-890, 899-901): "n m" then m pairs "u v", each pushed onto u's list ONLY -
+ *               a directed graph, not symmetrised.  oracle_build_csr_directed restates the flatten
+ *               loop (bfs.cu:910-916) for such tuples; oracle_bfs_serial then runs on it unchanged.
+ *   random form (bfs.cu:891-894, 902-906): srand(12345); u = rand() % n; v = rand() % n per edge, both
+ *               directions pushed.  oracle_random_edges draws the same tuples from the C library's
+ *               rand() - the stream is glibc's, the same library the reference links.
+ * ------------------------------------------------------------------------------------------- */
+int oracle_build_csr_directed(int64_t n, int64_t m, const int32_t* src, const int32_t* dst, int64_t* offsets,
+                              int32_t* sizes, int32_t* adj) {
+  memset(sizes, 0, (size_t)n * sizeof(int32_t));
+  for (int64_t i = 0; i < m; ++i) {
+    if (src[i] < 0 || dst[i] < 0 || src[i] >= n || dst[i] >= n) return ORACLE_ERR_RANGE;
+    sizes[src[i]]++;
+  }
+  int64_t run = 0;
+  for (int64_t v = 0; v < n; ++v) { offsets[v] = run; run += sizes[v]; }
+  int64_t* cur = (int64_t*)malloc((size_t)(n > 0 ? n : 1) * sizeof(int64_t));
+  if (!cur) return ORACLE_ERR_NOMEM;
+  memcpy(cur, offsets, (size_t)n * sizeof(int64_t));
+  for (int64_t i = 0; i < m; ++i) adj[cur[src[i]]++] = dst[i]; /* bfs.cu:901 */
+  free(cur);
+  return ORACLE_OK;
+}
+
+void oracle_random_edges(int64_t n, int64_t m, int32_t* src, int32_t* dst) {
+  srand(12345); /* bfs.cu:892 */
+  for (int64_t i = 0; i < m; ++i) {
+    src[i] = (int32_t)(rand() % n); /* bfs.cu:903 */
+    dst[i] = (int32_t)(rand() % n); /* bfs.cu:904 */
+  }
+}

@@ -28,6 +28,7 @@ extern Graph G;                                              // bfs.cu:28
 void readGraphFromFile(Graph& G, int argc, char** argv);     // bfs.cu:36, defined 829-880
 void bfsCPU(int start, Graph& G, std::vector<int>& distance, std::vector<int>& parent,
             std::vector<bool>& visited);                     // bfs.cu:37-38, defined 923-945
+void readGraph(Graph& G, int argc, char** argv);             // bfs.cu:35, defined 882-920 (dead code in the reference's main)
 
 extern "C" {
 
@@ -53,6 +54,28 @@ int ref_set_graph(int n, int e, const int* offsets, const int* sizes, const int*
   G.numVertices = n;
   G.numEdges = e;
   return 0;
+}
+
+// The reference's second reader in its stdin form (argc <= 2, bfs.cu:888): stdin is pointed at
+// `path` for the duration of the call.  Directed: "u v" is pushed onto u's list only (bfs.cu:901).
+int ref_read_graph_stdin(const char* path) {
+  G = Graph();
+  if (!freopen(path, "r", stdin)) return -1;
+  char a0[] = "ref", a1[] = "0";
+  char* argv[2] = {a0, a1};
+  readGraph(G, 2, argv);
+  return G.numVertices;
+}
+
+// ... and in its random form (bfs.cu:891-894): srand(12345), n = atoi(argv[2]), m = atoi(argv[3]).
+int ref_read_graph_random(int n, int m) {
+  G = Graph();
+  char a0[] = "ref", a1[] = "0", a2[32], a3[32];
+  snprintf(a2, sizeof(a2), "%d", n);
+  snprintf(a3, sizeof(a3), "%d", m);
+  char* argv[4] = {a0, a1, a2, a3};
+  readGraph(G, 4, argv);
+  return G.numVertices;
 }
 
 int ref_num_vertices() { return G.numVertices; }

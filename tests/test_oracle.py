@@ -263,3 +263,62 @@ def test_bounded_serial_search_is_a_prefix_of_the_full_one():
     assert 5000 <= scanned < 5000 + int(g.sizes.max()) + 1 and reached <= oracle.reach_stats(g, full)[0]
     seen = d != INT_MAX
     assert np.array_equal(d[seen], full[seen])  # whatever it labelled is labelled correctly
+
+
+# ---- the reference's second reader, readGraph (bfs.cu:882-920): stdin form (directed) and random form
+RG = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "readgraph")
+
+
+def _load_rg(name):
+    import json
+    with open(os.path.join(RG, name + ".json")) as f:
+        return json.load(f)
+
+
+def _same_csr(g, gold):
+    assert g.n == gold["n"] and g.num_edges == gold["num_edges"]
+    if gold["adj"] is not None:
+        assert g.offsets.tolist() == gold["offsets"] and g.sizes.tolist() == gold["sizes"] and g.adj.tolist() == gold["adj"]
+    chk = int((g.adj.astype(np.int64) * (np.arange(g.adj.size) % 1000003 + 1)).sum() % (2**61 - 1))
+    assert chk == gold["csr_checksum"]
+
+
+def test_directed_reader_restatement_matches_the_reference_vector():
+    gold = _load_rg("stdin40")
+    n, src, dst = oracle.read_edge_file(os.path.join(RG, "stdin40.txt"))
+    g = oracle.build_csr_directed(n, src, dst)
+    _same_csr(g, gold)  # rows in input order, arcs one way only (bfs.cu:901)
+    assert g.num_edges == gold["m"]
+    for s in gold["searches"]:
+        assert oracle.check_output(oracle.bfs_serial(g, s["root"]), np.array(s["depth"], np.int32)) == -1
+    assert (np.array(gold["searches"][-1]["depth"]) == INT_MAX).sum() == n - 1  # vertex 39 is a sink: it reaches nothing
+
+
+@pytest.mark.parametrize("n,m", [(50, 120), (3000, 9000)])
+def test_random_reader_restatement_matches_the_reference_vector(n, m):
+    gold = _load_rg(f"random_{n}_{m}")
+    src, dst = oracle.random_edges(n, m)  # srand(12345); rand() % n twice per edge (bfs.cu:892, 903-904)
+    g = oracle.build_csr(n, src, dst)     # both directions pushed (bfs.cu:905-906), as readGraphFromFile does
+    _same_csr(g, gold)
+    for s in gold["searches"]:
+        assert oracle.check_output(oracle.bfs_serial(g, s["root"]), np.array(s["depth"], np.int32)) == -1
+
+
+@pytest.mark.skipif(not oracle.ref_available(), reason="oracle/_ref not built (needs /root/reference)")
+def test_second_reader_against_the_live_reference(tmp_path):
+    rng = np.random.default_rng(5)
+    n, m = 300, 1200
+    s = rng.integers(0, n, m).astype(np.int32)
+    d = rng.integers(0, n, m).astype(np.int32)
+    p = str(tmp_path / "arcs.txt")
+    oracle.write_edge_file(p, n, s, d)
+    ref_g = oracle.ref_read_graph_stdin(p)
+    mine = oracle.build_csr_directed(n, s, d)
+    assert np.array_equal(ref_g.offsets, mine.offsets) and np.array_equal(ref_g.sizes, mine.sizes) and np.array_equal(ref_g.adj, mine.adj)
+    for root in (0, 17, 299):
+        depth, _ = oracle.ref_bfs_cpu(root, n)
+        assert oracle.check_output(oracle.bfs_serial(mine, root), depth) == -1
+    ref_g = oracle.ref_read_graph_random(777, 2500)
+    rs, rd = oracle.random_edges(777, 2500)
+    mine = oracle.build_csr(777, rs, rd)
+    assert np.array_equal(ref_g.offsets, mine.offsets) and np.array_equal(ref_g.adj, mine.adj)
