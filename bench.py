@@ -313,7 +313,8 @@ def run_ours(args):
         h = b2.Bfs(dev, dedup=int(not args.no_dedup))
     kind = KINDS[args.kind]
     h.set_option("mode", b2.MODE_TOP_DOWN if args.mode == "td" else b2.MODE_DIRECTION_OPT)
-    h.set_option("engine", b2.ENGINE_STEPWISE if args.engine == "stepwise" else b2.ENGINE_FUSED)
+    h.set_option("engine", {"fused": b2.ENGINE_FUSED, "stepwise": b2.ENGINE_STEPWISE, "scan": b2.ENGINE_SCAN,
+                            "pull": b2.ENGINE_PULL}[args.engine])
     peak, peak_kind = measured_peaks()
 
     def barrier():
@@ -426,7 +427,8 @@ def run_ours(args):
         d2h_mine = float(t.item())
     d2h_total = int(d2h_mine)
     multi_engine = h.get_option("multi_engine") if world > 1 else None
-    kernel = ("bfs_fused_kernel" if args.engine == "fused" else "stepwise phases") if world == 1 else \
+    kernel = {"fused": "bfs_fused_kernel", "stepwise": "stepwise phases", "scan": "scan engine (next_layer/count/scan/assign)",
+              "pull": "pull engine (pull_level_kernel)"}[args.engine] if world == 1 else \
         ("bfs_fused_multi_kernel (peer-memory engine, exchanges inside the kernel)" if multi_engine == 0 else
          "multi-rank phases (top_down_multi / bottom_up / apply_remote) + NCCL per level")
     s_teps = s_mr / (s_ms * 1e-3) / 1e9
@@ -600,7 +602,8 @@ def main():
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--root-seed", type=int, default=2)
     ap.add_argument("--mode", default="do", choices=["do", "td"])
-    ap.add_argument("--engine", default="fused", choices=["fused", "stepwise"])
+    ap.add_argument("--engine", default="fused", choices=["fused", "stepwise", "scan", "pull"],
+                    help="scan / pull: the reference's alternative strategies as comparators (one GPU)")
     ap.add_argument("--multi-engine", type=int, default=0, choices=[0, 1], help="several GPUs: 0 peer-memory kernel, 1 NCCL per level")
     ap.add_argument("--no-dedup", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU baseline AND the parity check")

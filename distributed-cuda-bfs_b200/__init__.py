@@ -24,7 +24,7 @@ HEADER_PATH = os.path.abspath(os.path.join(_HERE, "..", "include", "b2bfs.h"))
 INT_MAX = 2147483647
 KIND_RMAT, KIND_KRON, KIND_GRID = 0, 1, 2
 MODE_DIRECTION_OPT, MODE_TOP_DOWN = 0, 1
-ENGINE_FUSED, ENGINE_STEPWISE = 0, 1
+ENGINE_FUSED, ENGINE_STEPWISE, ENGINE_SCAN, ENGINE_PULL = 0, 1, 2, 3
 
 ERR_NAMES = {0: "OK", -1: "ERR_ARG", -2: "ERR_IO", -3: "ERR_FORMAT", -4: "ERR_RANGE", -5: "ERR_CUDA",
              -6: "ERR_NOMEM", -7: "ERR_STATE", -8: "ERR_COMM", -9: "ERR_UNSUPPORTED"}

@@ -34,6 +34,7 @@ struct b2bfs {
   BuiltCsr csr;
   // search state
   BatchState batch;  // allocated by the first b2bfs_run_batch on this graph
+  unsigned int* cmp_scratch = nullptr;  // comparator engines: n + n/1024 + 16 words, allocated on first use
   SearchView sv{};
   Control* pinned_ctl = nullptr;
   int grid = 0;
@@ -113,6 +114,8 @@ static void free_multi_state(b2bfs* h) {
 static void free_graph(b2bfs* h) {
   free_multi_state(h);
   free_batch(&h->batch);
+  cudaFree(h->cmp_scratch);
+  h->cmp_scratch = nullptr;
   cudaFree(h->d_src);
   cudaFree(h->d_dst);
   h->d_src = h->d_dst = nullptr;
@@ -460,7 +463,7 @@ int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
     h->directed = (int)value;
   }
   else if (k == "mode" && (value == B2BFS_MODE_DIRECTION_OPT || value == B2BFS_MODE_TOP_DOWN)) h->mode = (int)value;
-  else if (k == "engine" && (value == B2BFS_ENGINE_FUSED || value == B2BFS_ENGINE_STEPWISE)) h->engine = (int)value;
+  else if (k == "engine" && value >= B2BFS_ENGINE_FUSED && value <= B2BFS_ENGINE_PULL) h->engine = (int)value;
   else if (k == "gather_parent" && (value == 0 || value == 1)) h->gather_parent = (int)value;
   else if (k == "multi_engine" && (value == 0 || value == 1)) h->multi_engine = (int)value;
   else if (k == "alpha" && value >= 1 && value <= (1 << 20)) h->alpha = (int)value;
@@ -661,7 +664,16 @@ static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent
   MultiResult mr;
   API_CUDA(h, cudaEventRecord(h->ev0, h->stream));
   const bool p2p = multi && p.s.xbase[0] != nullptr;
-  Status s = p2p ? run_fused_multi(p, src, h->grid_multi, h->stream, &mr.launches)
+  const bool comparator = !multi && (h->engine == B2BFS_ENGINE_SCAN || h->engine == B2BFS_ENGINE_PULL);
+  const size_t cmp_totals_at = (size_t)h->n + 4;
+  if (comparator && !h->cmp_scratch)
+    API_CUDA(h, cudaMalloc(&h->cmp_scratch, (cmp_totals_at + (size_t)h->n / 1024 + 16) * sizeof(unsigned int)));
+  Status s = comparator ? (h->engine == B2BFS_ENGINE_SCAN
+                               ? run_scan_engine(p, src, h->grid, h->stream, h->pinned_ctl, h->cmp_scratch,
+                                                 h->cmp_scratch + cmp_totals_at, &launches)
+                               : run_pull_engine(p, src, h->grid, h->stream, h->pinned_ctl,
+                                                 reinterpret_cast<int*>(h->cmp_scratch), &launches))
+           : p2p ? run_fused_multi(p, src, h->grid_multi, h->stream, &mr.launches)
            : multi ? run_multi(p, h->mc, src, h->grid, h->stream, &mr)
            : (h->engine == B2BFS_ENGINE_FUSED) ? run_fused(p, src, h->grid, h->stream, &launches)
                                                : run_stepwise(p, src, h->grid, h->stream, h->pinned_ctl, &launches);

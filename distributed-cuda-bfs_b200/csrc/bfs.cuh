@@ -27,6 +27,12 @@ void launch_pack_stats(const BfsParams& p, int slot, unsigned long long* out, cu
 Status run_fused_multi(const BfsParams& p, int64_t src, int grid, cudaStream_t stream, int64_t* launches);
 Status multi_grid_size(int device, int* grid_out);
 
+// the reference's alternative strategies as comparator engines (comparators.cu)
+Status run_scan_engine(const BfsParams& p, int64_t src, int grid, cudaStream_t stream, Control* pinned,
+                       unsigned int* counts, unsigned int* block_totals, int64_t* launches);
+Status run_pull_engine(const BfsParams& p, int64_t src, int grid, cudaStream_t stream, Control* pinned,
+                       int* changed_dev, int64_t* launches);
+
 Status run_reach_stats(const BfsParams& p, const uint32_t* orig_deg, cudaStream_t stream, int64_t* launches);
 
 }  // namespace b2

@@ -948,6 +948,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
         st.level = rs->level; st.mode = rs->mode; st.fb = rs->fb; st.done = rs->done;
         st.cur_q = rs->cur_q; st.cur_wide = rs->cur_wide; st.prev_nf = rs->prev_nf;
         st.unexplored = rs->unexplored; st.td_levels = rs->td_levels; st.bu_levels = rs->bu_levels;
+        st.frontier_edges = rs->frontier_edges;  // every field: all CTAs must take the same decisions from here on
         cv = (Conversion)(*reinterpret_cast<const volatile int*>(&p.s.ctl->resume_conversion));
       }
       trace_mark(p.s.ctl, ntrace, st.level, 5);

@@ -95,6 +95,8 @@ struct LoopState {
   int td_levels, bu_levels;
 };
 
+static_assert(sizeof(LoopState) == 56, "new LoopState field: also copy it where the waiting CTAs catch up (bfs_fused_kernel)");
+
 constexpr int kTraceCap = 96;
 struct TraceRec {
   int level, phase;            // phase: 0 reset, 1 top-down, 2 bottom-up, 3 queue->bitmap, 4 bitmap->queue, 5 group levels

@@ -47,6 +47,11 @@ typedef struct b2bfs b2bfs_t;
 /* option "engine" */
 #define B2BFS_ENGINE_FUSED 0       /* whole search in ONE persistent cooperative kernel (default)  */
 #define B2BFS_ENGINE_STEPWISE 1    /* one launch per phase, host reads counters per level           */
+/* comparators: the reference's two alternative strategies, dead code in its main
+ * (bfs.cu:805-819), built here so the engines above can be measured against them; single GPU,
+ * top-down by nature, option "mode" is ignored */
+#define B2BFS_ENGINE_SCAN 2        /* runCudaScanBfs, bfs.cu:748-781: next queue by prefix sums, no tail atomic */
+#define B2BFS_ENGINE_PULL 3        /* multiBfs, bfs.cu:101-130, 475-539: all vertices inspected every level     */
 
 #define B2BFS_UNREACHED_DEPTH 2147483647 /* INT_MAX, bfs.cu:404, 793 */
 #define B2BFS_UNREACHED_PARENT (-1)
