@@ -26,7 +26,7 @@ struct b2bfs {
   std::string err;
   // options
   int dedup = 1, mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED;
-  int alpha = 14, beta = 24, gamma = 400, xvariant = 0, keep_edges = 1, gather_parent = 1, hub_first = 1, directed = 0;
+  int alpha = 14, beta = 24, gamma = 2000, xvariant = 0, keep_edges = 1, gather_parent = 1, hub_first = 1, directed = 0;
   // graph
   bool has_graph = false;
   int64_t n = 0, m = 0;
