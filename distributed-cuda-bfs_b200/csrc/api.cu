@@ -26,7 +26,7 @@ struct b2bfs {
   std::string err;
   // options
   int dedup = 1, mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED;
-  int alpha = 14, beta = 24, gamma = 2000, xvariant = 0, keep_edges = 1, gather_parent = 1, hub_first = 1, directed = 0;
+  int alpha = 14, beta = 24, gamma = 2000, xfullpush = 0, keep_edges = 1, gather_parent = 1, hub_first = 1, directed = 0;
   // graph
   bool has_graph = false;
   int64_t n = 0, m = 0;
@@ -264,7 +264,7 @@ static BfsParams make_params(const b2bfs* h) {
   p.tn.alpha = h->alpha;
   p.tn.beta = h->beta;
   p.tn.gamma = h->gamma;
-  p.tn.xvariant = h->xvariant;
+  p.tn.xfullpush = h->xfullpush;
   return p;
 }
 
@@ -469,7 +469,7 @@ int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
   else if (k == "alpha" && value >= 1 && value <= (1 << 20)) h->alpha = (int)value;
   else if (k == "beta" && value >= 1 && value <= (1 << 20)) h->beta = (int)value;
   else if (k == "gamma" && value >= 0 && value <= (1 << 20)) h->gamma = (int)value;
-  else if (k == "xvariant" && (value == 0 || value == 1)) h->xvariant = (int)value;
+  else if (k == "xfullpush" && (value == 0 || value == 1)) h->xfullpush = (int)value;
   else return fail(h, B2BFS_ERR_ARG, "unknown option or value out of range: " + k);
   return B2BFS_OK;
 }
@@ -486,7 +486,7 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   else if (k == "alpha") *value = h->alpha;
   else if (k == "beta") *value = h->beta;
   else if (k == "gamma") *value = h->gamma;
-  else if (k == "xvariant") *value = h->xvariant;
+  else if (k == "xfullpush") *value = h->xfullpush;
   else if (k == "grid") *value = h->grid;
   else if (k == "gather_parent") *value = h->gather_parent;
   else if (k == "multi_engine") *value = (h->world > 1 && h->p2p_ready && h->multi_engine == 0) ? 0 : 1;

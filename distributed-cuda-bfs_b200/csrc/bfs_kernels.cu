@@ -1018,31 +1018,22 @@ __device__ __forceinline__ volatile unsigned long long* xrecord(const BfsParams&
 // (narrow tail, wide tail, degree sum, bottom-up finds, source degree) of `slot`, sums[5..6] = this
 // rank's own tails and incoming[s] = pairs rank s staged for this rank.
 //
-// One exchange = one arrival atomic per CTA, one NVLink store burst, one poll:
+// One exchange = one arrival atomic per CTA, one burst of NVLink stores, one poll:
 //   * every CTA bumps an arrival counter (nth = number of this exchange in the kernel, 1-based; the
 //     host zeroes the counter before the launch);
 //   * the CTA that arrives LAST knows that everything this GPU wrote for its peers during the phase
 //     is on its way (the issuing warps fenced their own peer stores: remote_flush and
 //     push_frontier_slice end with __threadfence_system) and stores this rank's record into every
-//     rank's table, the epoch number last;
-//   * every CTA then polls ITS OWN table until the records of all ranks carry this epoch - nobody
-//     waits for a second, local release step.
+//     rank's table.  Every 64-bit word of a record carries the epoch in its upper 16 bits, so a word
+//     IS its own arrival flag: 13 independent stores per peer, no fence and no separate flag store
+//     behind them (a store + system fence + flag chain costs two more NVLink crossings);
+//   * every CTA then polls ITS OWN table, one thread per word, until the words of all ranks carry
+//     this epoch - nobody waits for a second, local release step.
 // `epoch` runs on across searches (Control::xepoch), so a slot of the 4-deep record ring is never
 // rewritten while a slower rank may still be reading it: to post epoch e+4 a rank must have
 // completed e+1..e+3, and completing e+1 needs every CTA of every rank to have arrived there, i.e.
-// to have finished reading e.
-__device__ __forceinline__ bool wait_for_records(const BfsParams& p, unsigned long long epoch, int from_rank) {
-  volatile unsigned long long* src = xrecord(p, p.g.rank, epoch, from_rank);
-  const unsigned long long t0 = global_ns();
-  while (src[31] != epoch) {
-    __nanosleep(40);
-    if (global_ns() - t0 > 4000000000ull) {  // 4 s: a peer died or never launched
-      p.s.ctl->error = 1;
-      return false;
-    }
-  }
-  return true;
-}
+// to have finished reading e.  A stale word of epoch e-4 cannot pass for e (tags differ by 4).
+constexpr unsigned long long kRecValueMask = (1ull << 48) - 1ull;  // counters stay far below 2^48
 
 __device__ __forceinline__ void cross_exchange(const BfsParams& p, unsigned long long epoch, unsigned long long nth,
                                                int slot, unsigned long long* sums, unsigned int* incoming, int* failed,
@@ -1051,6 +1042,9 @@ __device__ __forceinline__ void cross_exchange(const BfsParams& p, unsigned long
   __shared__ int last_s;
   const int k = p.g.world, me = p.g.rank;
   Control* ctl = p.s.ctl;
+  const unsigned long long tag = (epoch & 0xffffull) << 48;
+  const int r = threadIdx.x >> 4, w = threadIdx.x & 15;  // (rank, word) this thread posts / polls
+  const bool used = r < k && (w < 5 || w >= 8);
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();  // this CTA's counter atomics and local writes are ordered before its arrival
@@ -1061,48 +1055,41 @@ __device__ __forceinline__ void cross_exchange(const BfsParams& p, unsigned long
   __syncthreads();
   if (last_s) {
     if (threadIdx.x == 0 && trace_level >= 0) trace_put(ctl, trace_level, 11);  // every CTA of this GPU has arrived
-    if ((int)threadIdx.x < k) {
-      const int d = threadIdx.x;
+    if (used) {
       const LevelSlot* s = &ctl->slot[slot & 3];
-      volatile unsigned long long* dst = xrecord(p, d, epoch, me);
-      dst[0] = ld_volatile(&s->q_count);
-      dst[1] = ld_volatile(&s->wide_count);
-      dst[2] = ld_volatile(&s->edges);
-      dst[3] = ld_volatile(&s->bu_count);
-      dst[4] = (unsigned long long)ctl->src_degree;
-      for (int j = 0; j < 8; ++j) dst[8 + j] = j < k ? ld_volatile(&p.s.send_count[j * 32]) : 0u;
-      __threadfence_system();
-      dst[31] = epoch;  // arrival flag, after the payload
-    }
-    if (p.tn.xvariant == 1) {  // this CTA alone waits for the peers, then releases the others
-      if ((int)threadIdx.x < k) {
-        wait_for_records(p, epoch, threadIdx.x);
-        __threadfence_system();
+      unsigned long long v;
+      switch (w) {
+        case 0: v = ld_volatile(&s->q_count); break;
+        case 1: v = ld_volatile(&s->wide_count); break;
+        case 2: v = ld_volatile(&s->edges); break;
+        case 3: v = ld_volatile(&s->bu_count); break;
+        case 4: v = (unsigned long long)ctl->src_degree; break;
+        default: v = (w - 8) < k ? ld_volatile(&p.s.send_count[(w - 8) * 32]) : 0u; break;
       }
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        if (trace_level >= 0) trace_put(ctl, trace_level, 12);  // the records of all ranks are here
-        __threadfence();
-        *reinterpret_cast<volatile unsigned long long*>(&ctl->xrelease) = nth;
-      }
+      xrecord(p, r, epoch, me)[w] = (v & kRecValueMask) | tag;
     }
   }
-  if (p.tn.xvariant == 1) {
-    if (threadIdx.x == 0) {
-      while (ld_volatile(&ctl->xrelease) < nth) __nanosleep(20);
-      __threadfence();
+  if (used) {
+    volatile unsigned long long* src = xrecord(p, me, epoch, r) + w;
+    const unsigned long long t0 = global_ns();
+    unsigned long long x;
+    while (((x = *src) & ~kRecValueMask) != tag) {
+      __nanosleep(40);
+      if (global_ns() - t0 > 4000000000ull) {  // 4 s: a peer died or never launched
+        ctl->error = 1;
+        break;
+      }
     }
-  } else if ((int)threadIdx.x < k) {
-    wait_for_records(p, epoch, threadIdx.x);
-    __threadfence();  // the peers' payload stores were system-fenced before their flags left
+    rec_s[r][w] = x & kRecValueMask;
+    // acquire: what the peers wrote before their records is visible to this SM's later loads (a
+    // gpu-scope fence also drops the L1 lines that predate it: the frontier buffers are re-read)
+    if (w == 0) __threadfence();
   }
-  __syncthreads();
-  if ((int)threadIdx.x < k * 16) rec_s[threadIdx.x >> 4][threadIdx.x & 15] = xrecord(p, me, epoch, threadIdx.x >> 4)[threadIdx.x & 15];
   __syncthreads();
   for (int i = 0; i < 5; ++i) sums[i] = 0;
-  for (int r = 0; r < k; ++r) {
-    for (int i = 0; i < 5; ++i) sums[i] += rec_s[r][i];
-    incoming[r] = r == me ? 0u : (unsigned int)rec_s[r][8 + me];
+  for (int q = 0; q < k; ++q) {
+    for (int i = 0; i < 5; ++i) sums[i] += rec_s[q][i];
+    incoming[q] = q == me ? 0u : (unsigned int)rec_s[q][8 + me];
   }
   sums[5] = rec_s[me][0];
   sums[6] = rec_s[me][1];
@@ -1110,16 +1097,25 @@ __device__ __forceinline__ void cross_exchange(const BfsParams& p, unsigned long
   __syncthreads();
 }
 
-// copy this rank's next-frontier slice (bitmap[0]) into buffer `which` of every rank's frontier bitmap
+// copy this rank's next-frontier slice (bitmap[0]) into buffer `which` of every rank's frontier bitmap.
+// Only the 16-byte groups that DIFFER from what this rank stored there the last time are sent: every
+// rank's copy of my slice equals my own copy (all copies receive the same stores), so my own copy
+// tells what the peers hold.  Sparse levels (the first and the last bottom-up levels, a marking
+// top-down level) then move a few kilobytes instead of part/8 bytes to each of the k ranks.
 __device__ __forceinline__ void push_frontier_slice(const BfsParams& p, int which) {
   const int64_t words4 = p.g.part / 128;  // uint4 groups in a slice
   const uint4* mine = reinterpret_cast<const uint4*>(p.s.bitmap[0]);
   const int64_t tid = (int64_t)blockIdx.x * kBlock + threadIdx.x, nthreads = (int64_t)gridDim.x * kBlock;
   const size_t off = (size_t)which * xchg_frontier_bytes(p.g.world, p.g.part) + (size_t)p.g.rank * (size_t)p.g.part / 8;
-  for (int64_t i = tid; i < words4 * p.g.world; i += nthreads) {
-    const int d = (int)(i / words4);
-    const int64_t j = i - (int64_t)d * words4;
-    reinterpret_cast<uint4*>(p.s.xbase[d] + off)[j] = mine[j];
+  const uint4* held = reinterpret_cast<const uint4*>(p.s.xbase[p.g.rank] + off);
+  const bool full = p.tn.xfullpush != 0;
+  for (int64_t j = tid; j < words4; j += nthreads) {
+    const uint4 x = mine[j];
+    if (!full) {
+      const uint4 o = __ldcg(held + j);
+      if (x.x == o.x && x.y == o.y && x.z == o.z && x.w == o.w) continue;
+    }
+    for (int d = 0; d < p.g.world; ++d) reinterpret_cast<uint4*>(p.s.xbase[d] + off)[j] = x;
   }
   __threadfence_system();  // the slice is in every peer's memory before this thread reaches the exchange
 }
@@ -1286,7 +1282,6 @@ Status run_fused_multi(const BfsParams& p, int64_t src, int grid, cudaStream_t s
   void* args[] = {&pp, &s};
   // the arrival counter of the in-kernel exchanges starts from zero in every search
   B2_CUDA(cudaMemsetAsync(&p.s.ctl->xarrive, 0, sizeof(unsigned long long), stream));
-  B2_CUDA(cudaMemsetAsync(&p.s.ctl->xrelease, 0, sizeof(unsigned long long), stream));
   B2_CUDA(cudaLaunchCooperativeKernel((const void*)bfs_fused_multi_kernel, dim3(grid), dim3(kBlock), args, 0, stream));
   if (launches) *launches += 1;
   return Status();

@@ -114,7 +114,6 @@ struct Control {
   int error;                                             // peer-memory engine: a cross-GPU wait timed out
   alignas(128) unsigned long long xarrive;               // peer-memory engine: CTAs arrived at exchanges so far (this launch)
   alignas(128) unsigned long long xepoch;                // ... exchanges completed by all searches on this graph so far
-  alignas(128) unsigned long long xrelease;              // exchange variant 1: last exchange the polling CTA has completed
   unsigned int group_exit_seq;                           // bumped when the group leaves its level loop
   int trace_len;                                         // fused engine: per-phase timestamps of CTA 0
   TraceRec trace[kTraceCap];
@@ -157,7 +156,7 @@ struct Tuning {
   int alpha;                 // top-down -> bottom-up when m_f > m_u / alpha
   int beta;                  // bottom-up -> top-down when n_f < n / beta
   int gamma;                 // claim-only top-down level + forced switch when m_f * gamma > m_u / alpha (0: never)
-  int xvariant;              // peer-memory exchange: 0 every CTA polls the record table, 1 one CTA polls and releases the rest
+  int xfullpush;              // peer-memory engine: 1 = push whole frontier slices, 0 = only the 16-byte groups that changed
 };
 
 enum Conversion { kNoConversion = 0, kQueueToBitmap = 1, kBitmapToQueue = 2 };
