@@ -26,8 +26,18 @@
 //   --format auto|ref|mtx|snap|bin   how to read <edge_file> (default ref, the reference's format)
 //   --save-cache PATH     also write the tuples as a binary cache for the next run
 //   --device N
+//   --gpus N              the reference's second binary, `mpirun -np 2 ./osu_bw <src> <file>` (README.md:19-22,
+//                         bfs_mpi.cu:797-856), without MPI: the program starts N copies of itself, one per
+//                         GPU (devices 0..N-1), which partition the rows and search together over NVLink;
+//                         rank 0 prints the reference's lines and runs the self-check, as rank 0 does at
+//                         bfs_mpi.cu:826-847 (where the check is vacuous; here it is real).  N in 2..8.
+#include <sys/types.h>
+#include <sys/wait.h>
+#include <unistd.h>
+
 #include <chrono>
 #include <climits>
+#include <csignal>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -72,7 +82,51 @@ static bool all_digits(const char* s) {
   return true;
 }
 
+static int run_rank(int argc, char** argv, int rank, int world, const char* id_file);
+
+// --gpus N: start N copies of this program (ranks), hand them a file through which rank 0 publishes
+// the NCCL id, wait for all of them; the exit status is the worst of theirs
+static int launch_ranks(int argc, char** argv, int world) {
+  char id_file[128];
+  snprintf(id_file, sizeof(id_file), "/tmp/b2bfs_id_%d", (int)getpid());
+  unlink(id_file);
+  std::vector<pid_t> kids;
+  for (int r = 0; r < world; ++r) {
+    const pid_t pid = fork();  // before this process has touched CUDA
+    if (pid < 0) { perror("b2bfs: fork"); break; }
+    if (pid == 0) _exit(run_rank(argc, argv, r, world, id_file));
+    kids.push_back(pid);
+  }
+  int worst = (int)kids.size() == world ? 0 : 1;
+  for (size_t done = 0; done < kids.size(); ++done) {
+    int st = 0;
+    const pid_t pid = wait(&st);
+    if (pid < 0) break;
+    const int code = WIFEXITED(st) ? WEXITSTATUS(st) : 1;
+    if (code != 0 && worst == 0) {  // one rank failed: the others would wait for it forever
+      worst = code;
+      for (pid_t k : kids) if (k != pid) kill(k, SIGTERM);
+    }
+  }
+  unlink(id_file);
+  unlink((std::string(id_file) + ".go").c_str());
+  return worst;
+}
+
 int main(int argc, char** argv) {
+  for (int i = 1; i + 1 < argc; ++i) {
+    if (!strcmp(argv[i], "--gpus")) {
+      const int world = atoi(argv[i + 1]);
+      if (world == 1) break;
+      if (world < 2 || world > 8) { fprintf(stderr, "b2bfs: --gpus takes 1..8\n"); return 2; }
+      return launch_ranks(argc, argv, world);
+    }
+  }
+  return run_rank(argc, argv, 0, 1, nullptr);
+}
+
+static int run_rank(int argc, char** argv, int rank, int world, const char* id_file) {
+  const bool lead = rank == 0;  // the rank that talks (bfs_mpi.cu:826: `if (rank == 0)`)
   if (argc < 2) {
     fprintf(stderr, "usage: %s <src_vertex> <edge_file> | <src_vertex> --stdin | <src_vertex> --random N M\n"
                     "       [--no-check] [--dump-depth PATH] [--mode do|td] [--engine fused|stepwise] [--no-dedup] "
@@ -113,6 +167,7 @@ int main(int argc, char** argv) {
     else if (a == "--dump-depth" && i + 1 < argc) dump = argv[++i];
     else if (a == "--gen" && i + 1 < argc) gen = argv[++i];
     else if (a == "--device" && i + 1 < argc) device = atoi(argv[++i]);
+    else if (a == "--gpus" && i + 1 < argc) ++i;  // handled by main
     else if (a == "--save-cache" && i + 1 < argc) save_cache = argv[++i];
     else if (a == "--format" && i + 1 < argc) {
       const std::string f(argv[++i]);
@@ -125,8 +180,33 @@ int main(int argc, char** argv) {
   }
 
   b2bfs_t* h = nullptr;
-  int rc = b2bfs_create(&h, device);
-  if (rc) return die(nullptr, "b2bfs_create", rc);
+  int rc = 0;
+  if (world > 1) {
+    if (source == kStdin) { fprintf(stderr, "b2bfs: --stdin (a directed graph) runs on one GPU\n"); return 2; }
+    // rank 0 publishes the 128-byte NCCL id through a file, the others wait for it
+    unsigned char id[128];
+    const std::string tmp = std::string(id_file) + ".tmp";
+    if (lead) {
+      rc = b2bfs_comm_unique_id(id);
+      if (rc) return die(nullptr, "b2bfs_comm_unique_id", rc);
+      FILE* f = fopen(tmp.c_str(), "wb");
+      if (!f || fwrite(id, 1, 128, f) != 128 || fclose(f) != 0 || rename(tmp.c_str(), id_file) != 0) {
+        fprintf(stderr, "b2bfs: cannot publish the communicator id\n");
+        return 1;
+      }
+    } else {
+      FILE* f = nullptr;
+      for (int tries = 0; tries < 1200 && !(f = fopen(id_file, "rb")); ++tries) usleep(50000);
+      if (!f || fread(id, 1, 128, f) != 128) { fprintf(stderr, "b2bfs: rank %d never received the communicator id\n", rank); return 1; }
+      fclose(f);
+    }
+    rc = b2bfs_create_rank(&h, rank, rank, world, id);
+    if (rc) return die(nullptr, "b2bfs_create_rank", rc);
+    if (!lead && !freopen("/dev/null", "w", stdout)) return 1;  // only rank 0 prints the reference's lines
+  } else {
+    rc = b2bfs_create(&h, device);
+    if (rc) return die(nullptr, "b2bfs_create", rc);
+  }
   b2bfs_set_option(h, "dedup", dedup);
   b2bfs_set_option(h, "mode", mode);
   b2bfs_set_option(h, "engine", engine);
@@ -195,6 +275,7 @@ int main(int argc, char** argv) {
   }
 
   std::vector<int32_t> expected;
+  check = check && lead;
   if (check) {
     std::vector<int32_t> s(m), d(m);
     rc = b2bfs_copy_edges(h, 0, m, s.data(), d.data());
@@ -206,17 +287,29 @@ int main(int argc, char** argv) {
     printf("Elapsed time in milliseconds : %li ms.\n\n", ms);  // bfs.cu:218
   }
 
-  std::vector<int32_t> depth(n);
+  if (world > 1) {
+    // the ranks enter the collective search together: the others wait until rank 0 is through its
+    // host-side check (inside the search a rank that waits too long for a peer gives up)
+    const std::string go = std::string(id_file) + ".go";
+    if (lead) {
+      FILE* f = fopen(go.c_str(), "wb");
+      if (f) fclose(f);
+    } else {
+      for (int tries = 0; tries < 72000 && access(go.c_str(), F_OK) != 0; ++tries) usleep(50000);
+    }
+  }
+  std::vector<int32_t> depth(lead ? n : 0);
   b2bfs_stats st;
   printf("Starting queue parallel bfs.\n");  // bfs.cu:550
-  rc = b2bfs_run(h, start, depth.data(), nullptr, &st);
+  if (world > 1) b2bfs_set_option(h, "gather_parent", 0);
+  rc = b2bfs_run(h, start, lead ? depth.data() : nullptr, nullptr, &st);  // collective when world > 1
   if (rc) return die(h, "b2bfs_run", rc);
   printf("Elapsed time in milliseconds : %li ms.\n", (long)(st.search_ms + 0.5));  // bfs.cu:626
-  fprintf(stderr, "b2bfs: search %.3f ms on device, %d levels (%d top-down, %d bottom-up), %lld vertices reached, "
+  if (lead) fprintf(stderr, "b2bfs: search %.3f ms on device, %d levels (%d top-down, %d bottom-up), %lld vertices reached, "
                   "%.3f GTEPS\n", st.search_ms, st.levels, st.td_levels, st.bu_levels, (long long)st.reached_vertices,
           st.search_ms > 0 ? (st.reached_entries / 2) / (st.search_ms * 1e6) : 0.0);
 
-  if (dump) {
+  if (dump && lead) {
     FILE* f = fopen(dump, "w");
     if (!f) { fprintf(stderr, "b2bfs: cannot write %s\n", dump); b2bfs_destroy(h); return 1; }
     for (int64_t i = 0; i < n; ++i) fprintf(f, "%d\n", depth[i]);
