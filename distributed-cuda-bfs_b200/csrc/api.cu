@@ -26,7 +26,7 @@ struct b2bfs {
   std::string err;
   // options
   int dedup = 1, mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED;
-  int alpha = 14, beta = 24, gamma = 2000, xfullpush = 0, keep_edges = 1, gather_parent = 1, hub_first = 1, directed = 0;
+  int alpha = 14, beta = 24, gamma = 2000, huge_min = 4096, xfullpush = 0, keep_edges = 1, gather_parent = 1, hub_first = 1, directed = 0;
   // graph
   bool has_graph = false;
   int64_t n = 0, m = 0;
@@ -80,6 +80,8 @@ static void free_search_state(b2bfs* h) {
   cudaFree(h->sv.queue[1]);
   cudaFree(h->sv.wideq[0]);
   cudaFree(h->sv.wideq[1]);
+  cudaFree(h->sv.hugeq[0]);
+  cudaFree(h->sv.hugeq[1]);
   cudaFree(h->sv.ctl);
   h->sv = SearchView{};
 }
@@ -167,6 +169,11 @@ static int finish_load(b2bfs* h) {
   API_CUDA(h, cudaMalloc(&h->sv.queue[1], (size_t)(rows > 0 ? rows : 1) * sizeof(int32_t)));
   API_CUDA(h, cudaMalloc(&h->sv.wideq[0], wide_cap * sizeof(int2)));
   API_CUDA(h, cudaMalloc(&h->sv.wideq[1], wide_cap * sizeof(int2)));
+  if (!multi) {  // hub-row items: rows of >= 2 * kCtaChunk entries at the least, so E / kCtaChunk + E / (2 kCtaChunk) bounds them
+    const size_t huge_cap = (size_t)h->csr.entries / kCtaChunk + (size_t)h->csr.entries / (2 * kCtaChunk) + 16;
+    API_CUDA(h, cudaMalloc(&h->sv.hugeq[0], huge_cap * sizeof(int2)));
+    API_CUDA(h, cudaMalloc(&h->sv.hugeq[1], huge_cap * sizeof(int2)));
+  }
   API_CUDA(h, cudaMalloc(&h->sv.ctl, sizeof(Control)));
   API_CUDA(h, cudaMemsetAsync(h->sv.ctl, 0, sizeof(Control), h->stream));
   if (multi) {
@@ -264,6 +271,7 @@ static BfsParams make_params(const b2bfs* h) {
   p.tn.alpha = h->alpha;
   p.tn.beta = h->beta;
   p.tn.gamma = h->gamma;
+  p.tn.huge_min = h->huge_min;
   p.tn.xfullpush = h->xfullpush;
   return p;
 }
@@ -470,6 +478,7 @@ int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
   else if (k == "beta" && value >= 1 && value <= (1 << 20)) h->beta = (int)value;
   else if (k == "gamma" && value >= 0 && value <= (1 << 20)) h->gamma = (int)value;
   else if (k == "xfullpush" && (value == 0 || value == 1)) h->xfullpush = (int)value;
+  else if (k == "huge_min" && (value == 0 || (value >= 2 * kCtaChunk && value <= (1 << 30)))) h->huge_min = (int)value;
   else return fail(h, B2BFS_ERR_ARG, "unknown option or value out of range: " + k);
   return B2BFS_OK;
 }
@@ -487,6 +496,7 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   else if (k == "beta") *value = h->beta;
   else if (k == "gamma") *value = h->gamma;
   else if (k == "xfullpush") *value = h->xfullpush;
+  else if (k == "huge_min") *value = h->huge_min;
   else if (k == "grid") *value = h->grid;
   else if (k == "gather_parent") *value = h->gather_parent;
   else if (k == "multi_engine") *value = (h->world > 1 && h->p2p_ready && h->multi_engine == 0) ? 0 : 1;

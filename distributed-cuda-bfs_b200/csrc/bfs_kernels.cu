@@ -67,9 +67,34 @@ __device__ __forceinline__ void block_accumulate(unsigned long long x, unsigned 
   __syncthreads();
 }
 
+__device__ __forceinline__ unsigned int ld_volatile(const unsigned int* p) {
+  return *reinterpret_cast<const volatile unsigned int*>(p);
+}
+__device__ __forceinline__ unsigned long long ld_volatile(const unsigned long long* p) {
+  return *reinterpret_cast<const volatile unsigned long long*>(p);
+}
+
+// where hub rows go (the CTA-level bin); min == 0 switches the bin off
+struct HubOut {
+  int2* q;
+  unsigned int* count;
+  int64_t min;
+};
+__device__ __forceinline__ HubOut hub_out(const BfsParams& p, int level_of_items) {
+  HubOut h;
+  h.q = p.s.hugeq[level_of_items & 1];
+  h.count = &p.s.ctl->slot[level_of_items & 3].huge_count;
+  h.min = (h.q && p.g.world == 1) ? (int64_t)p.tn.huge_min : 0;
+  return h;
+}
+
 // Route a newly discovered vertex of degree d to the next level's work lists (lane-local).
-__device__ __forceinline__ void route_vertex(WarpStage& sg, int32_t v, int64_t d) {
-  if (d < kNarrow) {
+__device__ __forceinline__ void route_vertex(WarpStage& sg, int32_t v, int64_t d, const HubOut& hub) {
+  if (hub.min > 0 && d >= hub.min) {  // a handful of vertices per search: one tail atomic each is fine
+    const unsigned items = (unsigned)((d + kCtaChunk - 1) / kCtaChunk);
+    const unsigned base = atomicAdd(hub.count, items);
+    for (unsigned c = 0; c < items; ++c) hub.q[base + c] = make_int2(v, (int)c);
+  } else if (d < kNarrow) {
     sg.narrow[atomicAdd(&sg.ncnt, 1)] = v;
   } else {
     const int pos = atomicAdd(&sg.wcnt, 1);
@@ -180,12 +205,18 @@ __device__ __forceinline__ void phase_init(const BfsParams& p, int64_t src) {
     for (int k = 0; k < 4; ++k) {
       c->slot[k].q_count = 0;
       c->slot[k].wide_count = 0;
+      c->slot[k].huge_count = 0;
       c->slot[k].edges = 0;
       c->slot[k].bu_count = 0;
       c->slot[k].bu_cursor = 0;
     }
     const int64_t deg = src >= 0 ? p.g.rowptr[src + 1] - p.g.rowptr[src] : 0;  // src < 0: another rank owns it
+    const HubOut hub = hub_out(p, 0);
     if (src < 0) {
+    } else if (hub.min > 0 && deg >= hub.min) {
+      const unsigned items = (unsigned)((deg + kCtaChunk - 1) / kCtaChunk);
+      for (unsigned k = 0; k < items; ++k) hub.q[k] = make_int2((int)src, (int)k);
+      c->slot[0].huge_count = items;
     } else if (deg < kNarrow) {
       p.s.queue[0][0] = (int32_t)src;
       c->slot[0].q_count = 1;
@@ -207,8 +238,9 @@ __host__ __device__ inline LoopState initial_state(const BfsParams& p, int64_t s
   st.mode = 0;
   st.fb = 0;
   st.done = 0;
-  const bool wide = src_degree >= kNarrow;
-  st.cur_q = wide ? 0u : 1u;
+  const bool hub = p.s.hugeq[0] && p.g.world == 1 && p.tn.huge_min > 0 && src_degree >= p.tn.huge_min;
+  const bool wide = src_degree >= kNarrow && !hub;
+  st.cur_q = (wide || hub) ? 0u : 1u;
   st.cur_wide = wide ? (unsigned)((src_degree + kChunk - 1) / kChunk) : 0u;
   st.prev_nf = 1;
   st.unexplored = (unsigned long long)(p.g.entries - src_degree);
@@ -261,6 +293,48 @@ __device__ __forceinline__ void remote_flush(const BfsParams& p, RemoteStage& rs
   __syncwarp();
 }
 
+// ---------------------------------------------------------------------------------------------
+// CTA-level bin: the adjacency of a hub row reaches shared memory through the asynchronous copy
+// engine (cp.async.bulk, 1-D TMA; UBLKCP in SASS) behind an mbarrier, two buffers deep, so the
+// next chunk of kCtaChunk entries is in flight while the eight warps of the CTA probe and claim
+// the current one - no warp ever waits on a col[] load of its own.
+// ---------------------------------------------------------------------------------------------
+struct HubStage {
+  alignas(128) int32_t buf[2][kCtaChunk + 4];  // + 4: a chunk starts at a 16-byte boundary below its first entry
+  alignas(8) unsigned long long mbar[2];
+  int64_t rs[2], re[2];                        // entries [rs, re) of col are the chunk; buf holds [rs & ~3, ...)
+  int32_t u[2];
+  unsigned int seq;                            // items this CTA has consumed so far (buffer = seq & 1, parity = seq >> 1 & 1)
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void hub_stage_init(HubStage* hs) {  // one thread, once per kernel
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&hs->mbar[0])));
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&hs->mbar[1])));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  hs->seq = 0;
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t mbar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+               : "=r"(ok) : "r"(mbar), "r"(parity) : "memory");
+  return ok != 0;
+}
+// one thread: start the copy of item `it` of the frontier's hub list into buffer b
+__device__ __forceinline__ void hub_issue(const BfsParams& p, HubStage* hs, int b, const int2 it) {
+  const int64_t rs = __ldg(p.g.rowptr + it.x) + (int64_t)it.y * kCtaChunk;
+  const int64_t re = min(__ldg(p.g.rowptr + it.x + 1), rs + kCtaChunk);
+  const int64_t a0 = rs & ~(int64_t)3;
+  const uint32_t bytes = (uint32_t)(((re - a0 + 3) & ~(int64_t)3) * (int64_t)sizeof(int32_t));  // multiple of 16; col is padded
+  hs->u[b] = it.x;
+  hs->rs[b] = rs;
+  hs->re[b] = re;
+  const uint32_t mbar = smem_addr(&hs->mbar[b]);
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_addr(&hs->buf[b][0])), "l"(p.g.col + a0), "r"(bytes), "r"(mbar) : "memory");
+}
+
 // Four (u -> v) entries per lane at a time, phase by phase, so that the four visited probes, the
 // four claims and the four row-extent reads are each in flight together instead of forming one
 // long dependent chain per entry.  v and u are GLOBAL ids; with kMulti a vertex another rank owns is
@@ -268,7 +342,7 @@ __device__ __forceinline__ void remote_flush(const BfsParams& p, RemoteStage& rs
 template <bool kMulti>
 __device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpStage& sg, RemoteStage* rs,
                                           const int32_t (&v)[4], const int32_t (&u)[4], const bool (&valid)[4],
-                                          unsigned long long& edges_acc, bool mark, bool claim_only) {
+                                          unsigned long long& edges_acc, bool mark, bool claim_only, const HubOut& hub) {
   uint32_t word[4];
   bool c[4], local[4];
   int32_t vl[4];
@@ -323,7 +397,7 @@ __device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpSta
         p.s.depth[vl[k]] = level + 1;
         p.s.parent[vl[k]] = u[k];
         edges_acc += (unsigned long long)d[k];
-        route_vertex(sg, vl[k], d[k]);
+        route_vertex(sg, vl[k], d[k], hub);
         // the next level will most likely run bottom-up: leave the frontier bit behind now and
         // save the queue->bitmap pass and its grid-wide barrier
         if (mark) atomicOr(&p.s.bitmap[0][(uint32_t)vl[k] >> 5], 1u << (vl[k] & 31));
@@ -336,7 +410,8 @@ __device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpSta
 
 template <bool kMulti>
 __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopState& st, WarpStage* stage, int bid, int nb,
-                                               RemoteStage* rstage = nullptr, bool mark = false, bool claim_only = false) {
+                                               RemoteStage* rstage = nullptr, bool mark = false, bool claim_only = false,
+                                               HubStage* hs = nullptr) {
   const int level = st.level;
   const int32_t* q = p.s.queue[level & 1];
   const int2* wq = p.s.wideq[level & 1];
@@ -351,13 +426,46 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
 
   RemoteStage* rst = kMulti ? &rstage[threadIdx.x >> 5] : nullptr;
   const int32_t vbase = (int32_t)p.g.vbase;
+  const HubOut hub = hub_out(p, level + 1);
   if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
   if (kMulti && lane == 0) rst->cnt = 0;
   if (bid == 0 && threadIdx.x == 0) {  // recycle the slot two levels ahead
     LevelSlot* z = &p.s.ctl->slot[(level + 2) & 3];
-    z->q_count = 0; z->wide_count = 0; z->edges = 0; z->bu_count = 0; z->bu_cursor = 0;
+    z->q_count = 0; z->wide_count = 0; z->huge_count = 0; z->edges = 0; z->bu_count = 0; z->bu_cursor = 0;
   }
   __syncwarp();
+
+  // ---- hub rows first (they are the long poles): CTA items, block-uniform control flow
+  if (!kMulti && hs != nullptr) {
+    const int64_t nh = (int64_t)ld_volatile(&p.s.ctl->slot[level & 3].huge_count);  // final since the last barrier
+    const int2* hq = p.s.hugeq[level & 1];
+    unsigned seq = hs->seq;  // uniform: written back below, behind a block barrier
+    if (threadIdx.x == 0 && bid < nh) hub_issue(p, hs, seq & 1, __ldcg(hq + bid));
+    for (int64_t ci = bid; ci < nh; ci += nb) {
+      const int b = seq & 1;
+      if (threadIdx.x == 0 && ci + nb < nh) hub_issue(p, hs, b ^ 1, __ldcg(hq + ci + nb));  // next chunk in flight
+      while (!mbar_try_wait(smem_addr(&hs->mbar[b]), (seq >> 1) & 1)) {}
+      const int64_t rs = hs->rs[b], re = hs->re[b], a0 = rs & ~(int64_t)3;
+      const int32_t u = hs->u[b];
+      const int64_t w0 = (int64_t)(threadIdx.x >> 5) * (kCtaChunk / kWarpsPerBlock);
+      for (int64_t off = w0; off < w0 + kCtaChunk / kWarpsPerBlock; off += 128) {  // warp-uniform
+        const int64_t idx = off + 4 * lane;  // position in the buffer; entry a0 + idx of col
+        if (a0 + idx < re) {
+          const int4 x = *reinterpret_cast<const int4*>(&hs->buf[b][idx]);
+          const int32_t v[4] = {x.x, x.y, x.z, x.w};
+          const int32_t uu[4] = {u + vbase, u + vbase, u + vbase, u + vbase};
+          const int64_t e = a0 + idx;
+          const bool valid[4] = {e >= rs, e + 1 >= rs && e + 1 < re, e + 2 >= rs && e + 2 < re, e + 3 >= rs && e + 3 < re};
+          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only, hub);
+        }
+        stage_flush(sg, ns, nq, nwq, false);
+      }
+      __syncthreads();  // every warp is done with buffer b before it is refilled
+      ++seq;
+    }
+    if (threadIdx.x == 0) hs->seq = seq;
+    __syncthreads();
+  }
 
   const int64_t tiles = ((int64_t)st.cur_q + 31) >> 5;
   const int64_t work = tiles + (int64_t)st.cur_wide;
@@ -398,7 +506,7 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
           valid[j] = k < total;
           v[j] = valid[j] ? __ldg(p.g.col + ors + (k - oe)) : 0;
         }
-        td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only);
+        td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only, hub);
         stage_flush(sg, ns, nq, nwq, false);
         if (kMulti) remote_flush(p, *rst, false);
       }
@@ -416,7 +524,7 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
           const int32_t uu[4] = {u + vbase, u + vbase, u + vbase, u + vbase};
           const bool valid[4] = {base >= rs, base + 1 >= rs && base + 1 < re, base + 2 >= rs && base + 2 < re,
                                  base + 3 >= rs && base + 3 < re};
-          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only);
+          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only, hub);
         }
         stage_flush(sg, ns, nq, nwq, false);
         if (kMulti) remote_flush(p, *rst, false);
@@ -440,6 +548,7 @@ __device__ __forceinline__ void phase_apply_remote(const BfsParams& p, const Loo
   int2* nwq = p.s.wideq[(level + 1) & 1];
   LevelSlot* ns = &p.s.ctl->slot[(level + 1) & 3];
   WarpStage& sg = stage[threadIdx.x >> 5];
+  const HubOut hub = hub_out(p, level + 1);
   if (lane_id() == 0) { sg.ncnt = 0; sg.wcnt = 0; }
   __syncwarp();
   unsigned long long edges_acc = 0;
@@ -463,7 +572,7 @@ __device__ __forceinline__ void phase_apply_remote(const BfsParams& p, const Loo
         } else {
           const int64_t d = __ldg(p.g.rowptr + vl + 1) - __ldg(p.g.rowptr + vl);
           edges_acc += (unsigned long long)d;
-          route_vertex(sg, vl, d);
+          route_vertex(sg, vl, d, hub);
         }
         if (mark) atomicOr(&p.s.bitmap[0][w], bit);
       }
@@ -631,7 +740,7 @@ __device__ __forceinline__ void phase_bottom_up(const BfsParams& p, const LoopSt
 
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     LevelSlot* z = &p.s.ctl->slot[(level + 2) & 3];
-    z->q_count = 0; z->wide_count = 0; z->edges = 0; z->bu_count = 0; z->bu_cursor = 0;
+    z->q_count = 0; z->wide_count = 0; z->huge_count = 0; z->edges = 0; z->bu_count = 0; z->bu_cursor = 0;
   }
   if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
   __syncwarp();
@@ -721,6 +830,14 @@ __device__ __forceinline__ void phase_queue_to_bitmap(const BfsParams& p, const 
     const int2 it = wq[i];
     if (it.y == 0) atomicOr(&bm[(uint32_t)it.x >> 5], 1u << (it.x & 31));
   }
+  if (p.s.hugeq[0]) {
+    const int2* hq = p.s.hugeq[st.level & 1];
+    const int64_t nh = (int64_t)ld_volatile(&p.s.ctl->slot[st.level & 3].huge_count);
+    for (int64_t i = tid; i < nh; i += nthreads) {
+      const int2 it = hq[i];
+      if (it.y == 0) atomicOr(&bm[(uint32_t)it.x >> 5], 1u << (it.x & 31));
+    }
+  }
 }
 
 // take back the frontier bits a "marking" top-down level left in bitmap[0] when the search stays
@@ -735,6 +852,14 @@ __device__ __forceinline__ void phase_unmark(const BfsParams& p, const LoopState
     const int2 it = __ldcg(wq + i);
     if (it.y == 0) bm[(uint32_t)it.x >> 5] = 0;
   }
+  if (p.s.hugeq[0]) {
+    const int2* hq = p.s.hugeq[st.level & 1];
+    const int64_t nh = (int64_t)ld_volatile(&p.s.ctl->slot[st.level & 3].huge_count);
+    for (int64_t i = tid; i < nh; i += nthreads) {
+      const int2 it = __ldcg(hq + i);
+      if (it.y == 0) bm[(uint32_t)it.x >> 5] = 0;
+    }
+  }
 }
 
 // next bitmap (written by the bottom-up level that just ended) -> work lists of level st.level,
@@ -746,6 +871,7 @@ __device__ __forceinline__ void phase_bitmap_to_queue(const BfsParams& p, const 
   int32_t* q = p.s.queue[st.level & 1];
   int2* wq = p.s.wideq[st.level & 1];
   LevelSlot* cs = &p.s.ctl->slot[st.level & 3];
+  const HubOut hub = hub_out(p, st.level);
   const unsigned lane = lane_id();
   WarpStage& sg = stage[threadIdx.x >> 5];
   if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
@@ -769,7 +895,7 @@ __device__ __forceinline__ void phase_bitmap_to_queue(const BfsParams& p, const 
           const int b = __ffs(bits) - 1;
           bits &= bits - 1;
           const int64_t v = w * 32 + b;
-          route_vertex(sg, (int32_t)v, __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v));
+          route_vertex(sg, (int32_t)v, __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v), hub);
         }
       }
       stage_flush(sg, cs, q, wq, false);
@@ -784,7 +910,10 @@ __device__ __forceinline__ void phase_bitmap_to_queue(const BfsParams& p, const 
 __global__ void __launch_bounds__(kBlock) search_init_kernel(BfsParams p, int64_t src) { phase_init(p, src); }
 __global__ void __launch_bounds__(kBlock) top_down_kernel(BfsParams p, LoopState st, bool claim_only) {
   __shared__ WarpStage stage[kWarpsPerBlock];
-  phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x, nullptr, claim_only, claim_only);
+  __shared__ HubStage hub;
+  if (threadIdx.x == 0) hub_stage_init(&hub);
+  __syncthreads();
+  phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x, nullptr, claim_only, claim_only, &hub);
 }
 __global__ void __launch_bounds__(kBlock) bottom_up_kernel(BfsParams p, LoopState st) {
   __shared__ WarpStage stage[kWarpsPerBlock];
@@ -855,12 +984,6 @@ void launch_pack_stats(const BfsParams& p, int slot, unsigned long long* out, cu
 // counters, so no thread has to publish decisions.  Replaces the reference's per-level
 // launch / cudaDeviceSynchronize / managed-counter read / cudaMemset round trips (bfs.cu:569-619).
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned int ld_volatile(const unsigned int* p) {
-  return *reinterpret_cast<const volatile unsigned int*>(p);
-}
-__device__ __forceinline__ unsigned long long ld_volatile(const unsigned long long* p) {
-  return *reinterpret_cast<const volatile unsigned long long*>(p);
-}
 
 // Small frontiers (the first and last levels of a power-law search, EVERY level of a grid or road
 // graph): a full-grid barrier per level costs more than the level.  The first kGroupBlocks CTAs
@@ -903,8 +1026,16 @@ __device__ __forceinline__ void trace_mark(Control* c, int& n, int level, int ph
   if (blockIdx.x == 0 && threadIdx.x == 0) trace_put(c, level, phase);
 }
 
+// work items of the current frontier that only a full grid should take on: hub-row items
+__device__ __forceinline__ unsigned hub_items(const BfsParams& p, int level) {
+  return p.s.hugeq[0] ? ld_volatile(&p.s.ctl->slot[level & 3].huge_count) : 0u;
+}
+
 __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(BfsParams p, int64_t src) {
   __shared__ WarpStage stage[kWarpsPerBlock];
+  __shared__ HubStage hub;
+  if (threadIdx.x == 0) hub_stage_init(&hub);
+  __syncthreads();
   cg::grid_group grid = cg::this_grid();
   if (blockIdx.x == 0 && threadIdx.x == 0) p.s.ctl->trace_len = 0;
   phase_init(p, src);
@@ -919,7 +1050,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
   while (!st.done) {
     Conversion cv = kNoConversion;
     bool marked = false;
-    if (st.mode == 0 && frontier_work(st) <= kGroupMaxWork) {
+    if (st.mode == 0 && frontier_work(st) <= kGroupMaxWork && hub_items(p, st.level) == 0) {
       ++group_seq;
       if ((int)blockIdx.x < group) {
         do {
@@ -927,8 +1058,8 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
           group_barrier(&p.s.ctl->group_barrier, epoch, group);
           const LevelSlot* ns = &p.s.ctl->slot[(st.level + 1) & 3];
           cv = advance(st, p.tn, p.g.n, ld_volatile(&ns->q_count), ld_volatile(&ns->wide_count),
-                       ld_volatile(&ns->bu_count), ld_volatile(&ns->edges));
-        } while (!st.done && cv == kNoConversion && frontier_work(st) <= kGroupMaxWork);
+                       ld_volatile(&ns->bu_count), ld_volatile(&ns->edges), false, ld_volatile(&ns->huge_count));
+        } while (!st.done && cv == kNoConversion && frontier_work(st) <= kGroupMaxWork && hub_items(p, st.level) == 0);
         if (blockIdx.x == 0 && threadIdx.x == 0) {
           p.s.ctl->resume_state = st;
           p.s.ctl->resume_conversion = (int)cv;
@@ -956,13 +1087,13 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
       const int ph = st.mode == 0 ? 1 : 2;
       marked = st.mode == 0 && p.tn.mode == B2BFS_MODE_DIRECTION_OPT && st.bu_levels == 0 && st.level >= 1;
       const bool claim = claim_only_level(st, p.tn);  // implies marked
-      if (st.mode == 0) phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x, nullptr, marked, claim);
+      if (st.mode == 0) phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x, nullptr, marked, claim, &hub);
       else phase_bottom_up(p, st, stage);
       grid.sync();
       trace_mark(p.s.ctl, ntrace, st.level, claim ? 6 : ph);
       const LevelSlot* ns = &p.s.ctl->slot[(st.level + 1) & 3];
       cv = advance(st, p.tn, p.g.n, ld_volatile(&ns->q_count), ld_volatile(&ns->wide_count),
-                   ld_volatile(&ns->bu_count), ld_volatile(&ns->edges), claim);
+                   ld_volatile(&ns->bu_count), ld_volatile(&ns->edges), claim, ld_volatile(&ns->huge_count));
     }
     if (cv == kQueueToBitmap) {
       if (!marked) {  // a marking top-down level has already left the new frontier in bitmap[0]
@@ -1319,7 +1450,7 @@ Status run_stepwise(const BfsParams& p, int64_t src, int grid, cudaStream_t stre
     if (trace)
       fprintf(stderr, "[b2bfs]   found q=%u wide=%u bu=%llu edges=%llu\n", ns.q_count, ns.wide_count, ns.bu_count,
               ns.edges);
-    const Conversion cv = advance(st, p.tn, p.g.n, ns.q_count, ns.wide_count, ns.bu_count, ns.edges, claim);
+    const Conversion cv = advance(st, p.tn, p.g.n, ns.q_count, ns.wide_count, ns.bu_count, ns.edges, claim, ns.huge_count);
     if (cv == kQueueToBitmap) {
       if (!claim) {  // a claim-only level has left the new frontier in bitmap[0] itself
         queue_to_bitmap_kernel<<<grid, kBlock, 0, stream>>>(p, st);

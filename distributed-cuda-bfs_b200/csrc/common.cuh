@@ -16,6 +16,8 @@ constexpr int kWarpsPerBlock = kBlock / 32;
 constexpr int kSMs = 148;                // B200: 2 dies x 74 SMs; grids are sized in multiples of it
 constexpr int kNarrow = 32;              // rows narrower than this are gathered 32 at a time by one warp
 constexpr int kChunk = 128;              // wider rows are cut into work items of this many entries
+constexpr int kCtaChunk = 2048;          // rows of at least Tuning::huge_min entries: items of this many entries, one CTA
+                                         // each, staged into shared memory by a bulk asynchronous copy (TMA, 1-D)
 
 // ---------------------------------------------------------------------------------------------
 // error plumbing: every CUDA call is checked (the reference discards all return codes, bfs.cu:336)
@@ -72,6 +74,7 @@ struct GraphView {
 struct alignas(128) LevelSlot {
   alignas(128) unsigned int q_count;          // tail of the regular next queue
   alignas(128) unsigned int wide_count;       // tail of the wide-item next queue
+  alignas(128) unsigned int huge_count;       // tail of the CTA-item next queue (hub rows)
   alignas(128) unsigned long long edges;      // sum of degrees of the vertices found this level
   alignas(128) unsigned long long bu_count;   // vertices found by a bottom-up level
   alignas(128) unsigned long long bu_cursor;  // next unclaimed batch of bitmap words (dynamic balance)
@@ -126,6 +129,7 @@ struct SearchView {
   uint32_t* bitmap[2];       // frontier / next frontier, nwords each; all-zero while top-down runs
   int32_t* queue[2];         // narrow rows (degree < kNarrow): vertex ids, n each
   int2* wideq[2];            // wide rows: (vertex, chunk) work items of <= kChunk entries
+  int2* hugeq[2];            // hub rows: (vertex, chunk) work items of <= kCtaChunk entries (nullptr: bin not in use)
   Control* ctl;
   // multi-rank only (nullptr / 0 on a single GPU)
   uint32_t* gfrontier;       // world * part bits: the frontier of ALL ranks (allgathered), probed bottom-up
@@ -156,6 +160,7 @@ struct Tuning {
   int alpha;                 // top-down -> bottom-up when m_f > m_u / alpha
   int beta;                  // bottom-up -> top-down when n_f < n / beta
   int gamma;                 // claim-only top-down level + forced switch when m_f * gamma > m_u / alpha (0: never)
+  int huge_min;              // rows of at least this many entries go to the CTA-level bin (0: bin off)
   int xfullpush;              // peer-memory engine: 1 = push whole frontier slices, 0 = only the 16-byte groups that changed
 };
 
@@ -175,8 +180,8 @@ __host__ __device__ inline bool claim_only_level(const LoopState& st, const Tuni
 // `claimed`: the level that just ended was a claim-only one (nbu = its claims, nq/nwide/mf unused).
 __host__ __device__ inline Conversion advance(LoopState& st, const Tuning& tn, int64_t n, unsigned int nq,
                                               unsigned int nwide, unsigned long long nbu, unsigned long long mf,
-                                              bool claimed = false) {
-  const unsigned long long nf = (st.mode == 0 && !claimed) ? (unsigned long long)nq + nwide : nbu;
+                                              bool claimed = false, unsigned int nhuge = 0) {
+  const unsigned long long nf = (st.mode == 0 && !claimed) ? (unsigned long long)nq + nwide + nhuge : nbu;
   if (st.mode == 0) st.td_levels++; else st.bu_levels++;
   if (claimed) mf = 0;  // degrees of the discoveries were not read
   st.unexplored = (mf > st.unexplored) ? 0ull : st.unexplored - mf;

@@ -139,6 +139,23 @@ def test_claim_only_levels_change_no_depth(b2, kind, scale, ef, seed, gamma):
             _check_search(b2, h, g, int(r))
 
 
+@pytest.mark.parametrize("huge_min", [0, 4096])
+@pytest.mark.parametrize("kind,scale,seed", [(0, 17, 1), (1, 16, 5)])
+def test_hub_bin_changes_no_depth(b2, kind, scale, seed, huge_min):
+    """Rows of at least "huge_min" entries are expanded by whole CTAs from shared memory (bulk
+    asynchronous copies behind an mbarrier); 0 leaves them to the 128-entry warp items.  Same depths."""
+    n, s, d = oracle.generate_edges(kind, scale, 16, seed)
+    g = oracle.build_csr(n, s, d)
+    with b2.Bfs(0, huge_min=huge_min) as h:
+        h.generate(kind, scale, 16, seed)
+        assert h.get_option("max_degree") >= 4096  # the graph does have hub rows
+        hubs = np.argsort(g.sizes)[-3:]
+        rng = np.random.default_rng(seed)
+        roots = [int(hubs[-1]), int(hubs[0])] + [int(r) for r in rng.choice(np.flatnonzero(g.sizes > 0), 3, replace=False)]
+        for r in roots:  # a hub as the source, and sources whose first levels meet the hubs
+            _check_search(b2, h, g, r)
+
+
 def test_hub_rows_and_no_dedup(b2):
     """A star whose centre row is cut into many wide work items, plus duplicates and self-loops kept."""
     n = 20000
