@@ -338,10 +338,12 @@ def run_ours(args):
         """(filtered, strict) root lists, the same on every rank: row degrees and the giant-component
         mask are gathered collectively."""
         n = h.num_vertices
-        if args.no_dedup:
+        if args.no_dedup and world == 1:
             es, ed = h.edges()
             deg = nonloop_degree(n, es, ed)
             del es, ed
+        elif args.no_dedup:
+            deg = h.degrees()  # the multigraph's degrees (self-loops included), gathered over the ranks
         else:
             deg = h.row_degrees()
         h.run_collective(int(np.argmax(deg)), depth_out=pinned.array)  # untimed: membership of the largest component

@@ -313,7 +313,13 @@ class Bfs:
         self._check(lib().b2bfs_copy_row_degrees(self._h, out.ctypes.data))
         return out
 
-    def edges(self, first: int = 0, count: int | None = None):
+    def edges(self, first: int | None = None, count: int | None = None):
+        """Input tuples back to the host.  A rank of a multi-GPU job holds (and returns by default) only
+        its own share, tuples [tuples_first, tuples_first + tuples_count)."""
+        if first is None:
+            first = self.get_option("tuples_first")
+            if count is None:
+                count = self.get_option("tuples_count")
         if count is None:
             count = self.num_input_edges - first
         s = np.empty(count, np.int32)

@@ -30,6 +30,7 @@ struct b2bfs {
   // graph
   bool has_graph = false;
   int64_t n = 0, m = 0;
+  int64_t m_first = 0, m_loc = 0;  // the tuples this rank holds: [m_first, m_first + m_loc) (all of them on one GPU)
   int32_t *d_src = nullptr, *d_dst = nullptr;
   BuiltCsr csr;
   // search state
@@ -127,12 +128,93 @@ static void free_graph(b2bfs* h) {
   h->n = h->m = 0;
 }
 
+// which tuples this rank holds: all of them on one GPU, an m / world share on several
+static void set_tuple_share(b2bfs* h) {
+  h->m_first = h->world > 1 ? h->m * h->rank / h->world : 0;
+  h->m_loc = (h->world > 1 ? h->m * (h->rank + 1) / h->world : h->m) - h->m_first;
+}
+
 #define API_NCCL(h, expr)                                                                          \
   do {                                                                                             \
     ncclResult_t _r = (expr);                                                                      \
     if (_r != ncclSuccess)                                                                         \
       return fail(h, B2BFS_ERR_COMM, std::string(#expr) + ": " + (h)->mc.nccl->GetErrorString(_r)); \
   } while (0)
+
+// Several ranks: this rank's share of the tuples -> the CSR of this rank's rows.  Each tuple is
+// expanded where it lies, its two keys are bucketed by the rank that owns their row, the buckets are
+// exchanged over NVLink (grouped ncclSend / ncclRecv), and a rank sorts only what it owns.  Replaces
+// "every rank reads and keeps the whole graph" (bfs_mpi.cu:815, 832; bfs.cu:333-351).
+static int build_partitioned(b2bfs* h) {
+  const int k = h->world, me = h->rank;
+  const KeySpec ks = key_spec(h->n, h->part, h->hub_first, 0);
+  struct Temps {  // freed on every path
+    uint32_t* degc = nullptr;
+    unsigned long long* cursors = nullptr;
+    int* bad = nullptr;
+    uint64_t *send = nullptr, *ka = nullptr;
+    ~Temps() { cudaFree(degc); cudaFree(cursors); cudaFree(bad); cudaFree(send); cudaFree(ka); }
+  } t;
+  API_CUDA(h, cudaMalloc(&t.cursors, 16 * sizeof(unsigned long long)));
+  API_CUDA(h, cudaMalloc(&t.bad, sizeof(int)));
+  API_CUDA(h, cudaMemsetAsync(t.cursors, 0, 16 * sizeof(unsigned long long), h->stream));
+  API_CUDA(h, cudaMemsetAsync(t.bad, 0, sizeof(int), h->stream));
+  Status s;
+  if (ks.cbits) {  // degree class of every vertex: local counts, summed over the ranks
+    API_CUDA(h, cudaMalloc(&t.degc, (size_t)h->n * sizeof(uint32_t)));
+    API_CUDA(h, cudaMemsetAsync(t.degc, 0, (size_t)h->n * sizeof(uint32_t), h->stream));
+    s = count_degrees_device(h->d_src, h->d_dst, h->m_loc, h->n, t.degc, h->stream);
+    if (!s.ok()) return fail(h, s);
+    API_NCCL(h, h->mc.nccl->AllReduce(t.degc, t.degc, (size_t)h->n, ncclUint32, ncclSum, h->mc.comm, h->stream));
+    h->build_launches += 1;
+  }
+  // pass 1: how many keys for each owner; every rank learns the whole k x k matrix (+ a bad-id flag)
+  s = owner_keys_device(false, h->d_src, h->d_dst, h->m_loc, h->n, h->part, k, ks, t.degc, t.cursors, nullptr, t.bad, h->stream);
+  if (!s.ok()) return fail(h, s);
+  unsigned long long mine[16] = {0};
+  int bad_h = 0;
+  API_CUDA(h, cudaMemcpyAsync(mine, t.cursors, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+  API_CUDA(h, cudaMemcpyAsync(&bad_h, t.bad, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  API_CUDA(h, cudaStreamSynchronize(h->stream));
+  mine[8] = (unsigned long long)bad_h;
+  API_CUDA(h, cudaMemcpyAsync(h->mc.stats_send, mine, 16 * sizeof(unsigned long long), cudaMemcpyHostToDevice, h->stream));
+  API_NCCL(h, h->mc.nccl->AllGather(h->mc.stats_send, h->mc.stats_all, 16, ncclUint64, h->mc.comm, h->stream));
+  API_CUDA(h, cudaMemcpyAsync(h->mc.stats_host, h->mc.stats_all, (size_t)k * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+  API_CUDA(h, cudaStreamSynchronize(h->stream));
+  const unsigned long long* all = h->mc.stats_host;  // all[s * 16 + d] = keys rank s holds for rank d
+  for (int r = 0; r < k; ++r)
+    if (all[r * 16 + 8]) return fail(h, B2BFS_ERR_RANGE, "edge list holds a vertex id outside [0, vertex_num)");
+  // pass 2: keys into one bucket per owner
+  unsigned long long start[16] = {0}, total_send = 0;
+  for (int d = 0; d < k; ++d) { start[d] = total_send; total_send += mine[d]; }
+  API_CUDA(h, cudaMalloc(&t.send, (size_t)(total_send > 0 ? total_send : 1) * sizeof(uint64_t)));
+  API_CUDA(h, cudaMemcpyAsync(t.cursors, start, 8 * sizeof(unsigned long long), cudaMemcpyHostToDevice, h->stream));
+  s = owner_keys_device(true, h->d_src, h->d_dst, h->m_loc, h->n, h->part, k, ks, t.degc, t.cursors, t.send, t.bad, h->stream);
+  if (!s.ok()) return fail(h, s);
+  h->build_launches += 2;
+  // exchange: bucket d of rank s lands in rank d's key array at the offset of s
+  unsigned long long N = 0, at[16] = {0};
+  for (int r = 0; r < k; ++r) { at[r] = N; N += all[r * 16 + me]; }
+  API_CUDA(h, cudaMalloc(&t.ka, (size_t)(N > 0 ? N : 1) * sizeof(uint64_t)));
+  API_NCCL(h, h->mc.nccl->GroupStart());
+  for (int r = 0; r < k; ++r) {
+    if (r == me) continue;
+    if (mine[r]) API_NCCL(h, h->mc.nccl->Send(t.send + start[r], (size_t)mine[r], ncclUint64, r, h->mc.comm, h->stream));
+    if (all[r * 16 + me]) API_NCCL(h, h->mc.nccl->Recv(t.ka + at[r], (size_t)all[r * 16 + me], ncclUint64, r, h->mc.comm, h->stream));
+  }
+  API_NCCL(h, h->mc.nccl->GroupEnd());
+  if (mine[me])
+    API_CUDA(h, cudaMemcpyAsync(t.ka + at[me], t.send + start[me], (size_t)mine[me] * sizeof(uint64_t), cudaMemcpyDeviceToDevice, h->stream));
+  API_CUDA(h, cudaStreamSynchronize(h->stream));
+  cudaFree(t.send); t.send = nullptr;
+  cudaFree(t.degc); t.degc = nullptr;
+  uint64_t* ka = t.ka;
+  t.ka = nullptr;  // build_csr_from_keys owns it from here
+  s = build_csr_from_keys(ka, (int64_t)N, h->n, h->vbase, h->vbase + h->nloc, ks, h->dedup, 0, h->part / 32, h->stream, &h->csr,
+                          &h->build_launches);
+  if (!s.ok()) return fail(h, s);
+  return B2BFS_OK;
+}
 
 // edges are in d_src/d_dst: build the CSR (this rank's rows) and the per-search buffers
 static int finish_load(b2bfs* h) {
@@ -147,11 +229,17 @@ static int finish_load(b2bfs* h) {
     h->vbase = 0;
     h->nloc = h->n;
   }
-  Status s = build_csr_device(h->d_src, h->d_dst, h->m, h->n, h->vbase, h->vbase + h->nloc, multi, h->dedup,
-                              h->hub_first, h->directed, multi ? h->part / 32 : 0, h->stream, &h->csr, &h->build_launches);
-  if (!s.ok()) {
-    free_graph(h);
-    return fail(h, s);
+  Status s;
+  if (!multi) {
+    s = build_csr_device(h->d_src, h->d_dst, h->m, h->n, h->dedup, h->hub_first, h->directed, h->stream, &h->csr,
+                         &h->build_launches);
+    if (!s.ok()) {
+      free_graph(h);
+      return fail(h, s);
+    }
+  } else {
+    const int rc = build_partitioned(h);
+    if (rc) { free_graph(h); return rc; }
   }
   if (!h->keep_edges) {
     cudaFree(h->d_src);
@@ -504,6 +592,8 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   else if (k == "world") *value = h->world;
   else if (k == "local_rows") *value = h->nloc;
   else if (k == "part") *value = h->part;
+  else if (k == "tuples_first") *value = h->m_first;
+  else if (k == "tuples_count") *value = h->m_loc;
   else if (k == "wide_items") *value = h->csr.wide_items;
   else if (k == "max_degree") *value = h->csr.max_degree;
   else if (k == "build_launches") *value = h->build_launches;
@@ -519,12 +609,14 @@ int b2bfs_load_edges(b2bfs_t* h, int64_t n, int64_t m, const int32_t* src, const
   free_graph(h);
   h->n = n;
   h->m = m;
-  const size_t bytes = (size_t)(m > 0 ? m : 1) * sizeof(int32_t);
+  set_tuple_share(h);  // several ranks: every rank is handed all m tuples (as every MPI rank of the reference parses
+                       // the whole file, bfs_mpi.cu:815) but takes only its share of them to the device
+  const size_t bytes = (size_t)(h->m_loc > 0 ? h->m_loc : 1) * sizeof(int32_t);
   API_CUDA(h, cudaMalloc(&h->d_src, bytes));
   API_CUDA(h, cudaMalloc(&h->d_dst, bytes));
-  if (m > 0) {
-    API_CUDA(h, cudaMemcpyAsync(h->d_src, src, (size_t)m * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
-    API_CUDA(h, cudaMemcpyAsync(h->d_dst, dst, (size_t)m * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+  if (h->m_loc > 0) {
+    API_CUDA(h, cudaMemcpyAsync(h->d_src, src + h->m_first, (size_t)h->m_loc * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    API_CUDA(h, cudaMemcpyAsync(h->d_dst, dst + h->m_first, (size_t)h->m_loc * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
   }
   return finish_load(h);
 }
@@ -555,6 +647,7 @@ void b2bfs_free_edges(int32_t* src, int32_t* dst) { free_tuples(false, src, dst)
 int b2bfs_save_edge_cache(b2bfs_t* h, const char* path) {
   if (!h || !path) return fail(h, B2BFS_ERR_ARG, "b2bfs_save_edge_cache: null argument");
   if (!h->has_graph || !h->d_src) return fail(h, B2BFS_ERR_STATE, "input tuples are not resident (keep_edges=0?)");
+  if (h->world > 1) return fail(h, B2BFS_ERR_UNSUPPORTED, "a rank of a multi-GPU job holds only its share of the tuples: save the cache from a single-GPU handle");
   API_CUDA(h, cudaSetDevice(h->device));
   FILE* f = fopen(path, "wb");
   if (!f) return fail(h, B2BFS_ERR_IO, std::string("cannot write ") + path);
@@ -577,9 +670,10 @@ int b2bfs_generate(b2bfs_t* h, int kind, int scale, int edgefactor, uint64_t see
   free_graph(h);
   h->n = b2_gen_num_vertices(kind, scale);
   h->m = b2_gen_num_edges(kind, scale, edgefactor);
-  API_CUDA(h, cudaMalloc(&h->d_src, (size_t)h->m * sizeof(int32_t)));
-  API_CUDA(h, cudaMalloc(&h->d_dst, (size_t)h->m * sizeof(int32_t)));
-  Status s = generate_edges_device(kind, scale, edgefactor, seed, 0, h->m, h->d_src, h->d_dst, h->stream);
+  set_tuple_share(h);  // several ranks: each generates its own m / world tuples of the stream
+  API_CUDA(h, cudaMalloc(&h->d_src, (size_t)(h->m_loc > 0 ? h->m_loc : 1) * sizeof(int32_t)));
+  API_CUDA(h, cudaMalloc(&h->d_dst, (size_t)(h->m_loc > 0 ? h->m_loc : 1) * sizeof(int32_t)));
+  Status s = generate_edges_device(kind, scale, edgefactor, seed, h->m_first, h->m_loc, h->d_src, h->d_dst, h->stream);
   if (!s.ok()) { free_graph(h); return fail(h, s); }
   h->build_launches += 1;
   return finish_load(h);
@@ -642,9 +736,12 @@ int b2bfs_copy_edges(b2bfs_t* h, int64_t first, int64_t count, int32_t* src_out,
   if (!h || !src_out || !dst_out) return fail(h, B2BFS_ERR_ARG, "null argument");
   if (!h->has_graph || !h->d_src) return fail(h, B2BFS_ERR_STATE, "input tuples are not resident (keep_edges=0?)");
   if (first < 0 || count < 0 || first + count > h->m) return fail(h, B2BFS_ERR_ARG, "tuple range out of bounds");
+  if (first < h->m_first || first + count > h->m_first + h->m_loc)
+    return fail(h, B2BFS_ERR_ARG, "tuple range not held by this rank: it keeps tuples [" + std::to_string(h->m_first) + ", " +
+                                      std::to_string(h->m_first + h->m_loc) + ") (options \"tuples_first\" / \"tuples_count\")");
   API_CUDA(h, cudaSetDevice(h->device));
-  API_CUDA(h, cudaMemcpy(src_out, h->d_src + first, (size_t)count * sizeof(int32_t), cudaMemcpyDeviceToHost));
-  API_CUDA(h, cudaMemcpy(dst_out, h->d_dst + first, (size_t)count * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  API_CUDA(h, cudaMemcpy(src_out, h->d_src + (first - h->m_first), (size_t)count * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  API_CUDA(h, cudaMemcpy(dst_out, h->d_dst + (first - h->m_first), (size_t)count * sizeof(int32_t), cudaMemcpyDeviceToHost));
   return B2BFS_OK;
 }
 

@@ -447,8 +447,8 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
       while (!mbar_try_wait(smem_addr(&hs->mbar[b]), (seq >> 1) & 1)) {}
       const int64_t rs = hs->rs[b], re = hs->re[b], a0 = rs & ~(int64_t)3;
       const int32_t u = hs->u[b];
-      const int64_t w0 = (int64_t)(threadIdx.x >> 5) * (kCtaChunk / kWarpsPerBlock);
-      for (int64_t off = w0; off < w0 + kCtaChunk / kWarpsPerBlock; off += 128) {  // warp-uniform
+      // the buffer holds re - a0 <= kCtaChunk + 3 positions: 128 per warp and round, rounds strided over the warps
+      for (int64_t off = (int64_t)(threadIdx.x >> 5) * 128; off < re - a0; off += kWarpsPerBlock * 128) {  // warp-uniform
         const int64_t idx = off + 4 * lane;  // position in the buffer; entry a0 + idx of col
         if (a0 + idx < re) {
           const int4 x = *reinterpret_cast<const int4*>(&hs->buf[b][idx]);

@@ -46,6 +46,7 @@
 #include <vector>
 
 #include "../../include/b2bfs.h"
+#include "../../include/b2bfs_graphgen.h"
 
 static int die(b2bfs_t* h, const char* what, int rc) {
   fprintf(stderr, "b2bfs: %s failed (%d): %s\n", what, rc, b2bfs_last_error(h));
@@ -181,6 +182,8 @@ static int run_rank(int argc, char** argv, int rank, int world, const char* id_f
 
   b2bfs_t* h = nullptr;
   int rc = 0;
+  int gen_kind = 0, gen_scale = 0, gen_ef = 16;
+  unsigned long long gen_seed = 1;
   if (world > 1) {
     if (source == kStdin) { fprintf(stderr, "b2bfs: --stdin (a directed graph) runs on one GPU\n"); return 2; }
     // rank 0 publishes the 128-byte NCCL id through a file, the others wait for it
@@ -244,6 +247,7 @@ static int run_rank(int argc, char** argv, int rank, int world, const char* id_f
     unsigned long long seed = 1;
     if (sscanf(gen, "%15[a-z]:%d:%d:%llu", kind, &scale, &ef, &seed) < 2) { fprintf(stderr, "b2bfs: bad --gen\n"); return 2; }
     const int k = !strcmp(kind, "kron") ? B2BFS_KIND_KRON : !strcmp(kind, "grid") ? B2BFS_KIND_GRID : B2BFS_KIND_RMAT;
+    gen_kind = k; gen_scale = scale; gen_ef = ef; gen_seed = seed;
     rc = b2bfs_generate(h, k, scale, ef, seed);
     if (rc) return die(h, "b2bfs_generate", rc);
   } else {
@@ -278,8 +282,28 @@ static int run_rank(int argc, char** argv, int rank, int world, const char* id_f
   check = check && lead;
   if (check) {
     std::vector<int32_t> s(m), d(m);
-    rc = b2bfs_copy_edges(h, 0, m, s.data(), d.data());
-    if (rc) return die(h, "b2bfs_copy_edges", rc);
+    if (world == 1) {
+      rc = b2bfs_copy_edges(h, 0, m, s.data(), d.data());
+      if (rc) return die(h, "b2bfs_copy_edges", rc);
+    } else if (gen) {  // a rank holds only its share of the tuples on the device: the host draws the same stream
+      for (int64_t i = 0; i < m; ++i) {
+        uint32_t u, v;
+        b2_gen_edge(gen_kind, gen_scale, gen_ef, gen_seed, (uint64_t)i, &u, &v);
+        s[i] = (int32_t)u;
+        d[i] = (int32_t)v;
+      }
+    } else if (source == kRandom) {
+      srand(12345);
+      for (int64_t i = 0; i < m; ++i) { s[i] = (int32_t)(rand() % n); d[i] = (int32_t)(rand() % n); }
+    } else {
+      int64_t fn = 0, fm = 0;
+      int32_t *fs = nullptr, *fd = nullptr;
+      rc = b2bfs_read_graph_file(path, format, &fn, &fm, &fs, &fd);
+      if (rc || fm != m) return die(nullptr, "b2bfs_read_graph_file", rc);
+      memcpy(s.data(), fs, (size_t)m * sizeof(int32_t));
+      memcpy(d.data(), fd, (size_t)m * sizeof(int32_t));
+      b2bfs_free_edges(fs, fd);
+    }
     printf("Starting sequential bfs.\n");  // bfs.cu:213
     const auto t0 = std::chrono::steady_clock::now();
     host_check_bfs(n, m, s, d, start, expected, source == kStdin);

@@ -119,6 +119,55 @@ __global__ void __launch_bounds__(kBlock) count_owned_kernel(const int32_t* __re
 }
 
 // ---------------------------------------------------------------------------------------------
+// several ranks: every rank holds only ITS share of the tuples (m / world of them).  A tuple (u,v)
+// yields the key of entry u -> v for owner(u) and of v -> u for owner(v); pass 1 counts the keys per
+// owner, pass 2 writes them into one bucket per owner (one warp-aggregated cursor atomic per owner
+// and warp), and the buckets travel to their owners over NVLink (multi.cu, exchange_owner_keys).
+// Replaces "every rank reads the whole graph and keeps what it owns" (bfs_mpi.cu:815, and round 1 here).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t class_bits(const uint32_t* degc, int64_t v, int vbits) {
+  return degc ? (uint64_t)(15 - min(15, 31 - __clz((int)max(degc[v], 1u)))) << vbits : 0ull;
+}
+
+template <bool kWrite>
+__global__ void __launch_bounds__(kBlock) owner_keys_kernel(const int32_t* __restrict__ src, const int32_t* __restrict__ dst,
+                                                            int64_t m, int64_t n, int64_t part, int world, int vbits, int rshift,
+                                                            const uint32_t* __restrict__ degc,
+                                                            unsigned long long* __restrict__ cursors /* world, zeroed (count) or bucket starts (write) */,
+                                                            uint64_t* __restrict__ keys, int* bad_flag) {
+  const unsigned lane = threadIdx.x & 31;
+  const int64_t stride = (int64_t)gridDim.x * kBlock;
+  const int64_t rounds = (2 * m + stride - 1) / stride;
+  for (int64_t r = 0; r < rounds; ++r) {  // one (tuple, direction) per thread and round; warp-uniform trip count
+    const int64_t t = r * stride + (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    int owner = -1;
+    uint64_t key = 0;
+    if (t < 2 * m) {
+      const int64_t i = t >> 1;
+      int64_t u = src[i], v = dst[i];
+      if (u < 0 || v < 0 || u >= n || v >= n) {
+        *bad_flag = 1;
+      } else {
+        if (t & 1) { const int64_t x = u; u = v; v = x; }
+        owner = (int)(u / part);
+        if (kWrite) key = ((uint64_t)(u - (int64_t)owner * part) << rshift) | class_bits(degc, v, vbits) | (uint64_t)v;
+      }
+    }
+    for (int d = 0; d < world; ++d) {
+      const unsigned mk = __ballot_sync(0xffffffffu, owner == d);
+      if (!mk) continue;
+      unsigned long long base = 0;
+      const int leader = __ffs(mk) - 1;
+      if ((int)lane == leader) base = atomicAdd(&cursors[d], (unsigned long long)__popc(mk));
+      if (kWrite) {
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (owner == d) keys[base + __popc(mk & ((1u << lane) - 1u))] = key;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // sorted keys -> col[] + rowptr[] (+ the undeduplicated row boundaries)
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool keep_entry(const uint64_t key, const uint64_t prev, bool first, int dedup, int vbits,
@@ -255,66 +304,95 @@ static int bits_for(int64_t n) {
   return b;
 }
 
-Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64_t n, int64_t row_begin,
-                        int64_t row_end, bool partitioned, int dedup, int hub_first, int directed,
-                        int64_t nwords_override, cudaStream_t stream,
-                        BuiltCsr* out, int64_t* launches) {
+KeySpec key_spec(int64_t n, int64_t max_rows_per_rank, int hub_first, int directed) {
+  KeySpec k;
+  k.vbits = bits_for(n);
+  const int rbits = bits_for(max_rows_per_rank > 0 ? max_rows_per_rank : 1);
+  k.cbits = (hub_first && !directed && k.vbits + rbits + 4 <= 64) ? 4 : 0;
+  k.rshift = k.vbits + k.cbits;
+  return k;
+}
+
+static int tuple_grid(int64_t m) {
+  const int64_t eblocks = (m + kBlock - 1) / kBlock;
+  return (int)(eblocks < (int64_t)kSMs * 16 ? (eblocks > 0 ? eblocks : 1) : (int64_t)kSMs * 16);
+}
+
+Status count_degrees_device(const int32_t* src, const int32_t* dst, int64_t m, int64_t n, uint32_t* degc, cudaStream_t stream) {
+  degree_count_kernel<<<tuple_grid(m), kBlock, 0, stream>>>(src, dst, m, n, degc);
+  B2_CUDA(cudaGetLastError());
+  return Status();
+}
+
+Status owner_keys_device(bool write, const int32_t* src, const int32_t* dst, int64_t m, int64_t n, int64_t part, int world,
+                         const KeySpec& ks, const uint32_t* degc, unsigned long long* cursors, uint64_t* keys, int* bad_flag,
+                         cudaStream_t stream) {
+  const int grid = tuple_grid(2 * m);
+  if (write)
+    owner_keys_kernel<true><<<grid, kBlock, 0, stream>>>(src, dst, m, n, part, world, ks.vbits, ks.rshift, degc, cursors, keys, bad_flag);
+  else
+    owner_keys_kernel<false><<<grid, kBlock, 0, stream>>>(src, dst, m, n, part, world, ks.vbits, ks.rshift, degc, cursors, keys, bad_flag);
+  B2_CUDA(cudaGetLastError());
+  return Status();
+}
+
+// one GPU: all 2m (or m, directed) keys of the tuples, then build_csr_from_keys
+Status build_csr_device(const int32_t* src, const int32_t* dst, int64_t m, int64_t n, int dedup, int hub_first, int directed,
+                        cudaStream_t stream, BuiltCsr* out, int64_t* launches) {
+  *out = BuiltCsr();
+  const KeySpec ks = key_spec(n, n, hub_first, directed);
+  DeviceTemps temps;
+  int* bad = nullptr;
+  B2_CUDA(temps.alloc(&bad, sizeof(int)));
+  B2_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), stream));
+  const int64_t N = directed ? m : 2 * m;
+  uint64_t* ka = nullptr;
+  B2_CUDA(cudaMalloc(&ka, (size_t)(N > 0 ? N : 1) * sizeof(uint64_t)));  // handed over to build_csr_from_keys
+  uint32_t* degc = nullptr;
+  if (ks.cbits) {
+    if (cudaMalloc(&degc, (size_t)n * sizeof(uint32_t)) != cudaSuccess) { cudaFree(ka); return make_error(B2BFS_ERR_NOMEM, "degree classes"); }
+    temps.ptrs[temps.count++] = degc;
+    cudaMemsetAsync(degc, 0, (size_t)n * sizeof(uint32_t), stream);
+    degree_count_kernel<<<tuple_grid(m), kBlock, 0, stream>>>(src, dst, m, n, degc);
+    if (launches) *launches += 1;
+  }
+  expand_edges_kernel<<<tuple_grid(m), kBlock, 0, stream>>>(src, dst, m, n, ks.vbits, ks.rshift, degc, 0, n, ka, nullptr, bad, directed);
+  if (launches) *launches += 1;
+  int bad_h = 0;
+  cudaError_t e = cudaMemcpyAsync(&bad_h, bad, sizeof(int), cudaMemcpyDeviceToHost, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  if (e != cudaSuccess || bad_h) {
+    cudaFree(ka);
+    if (e != cudaSuccess) return make_error(B2BFS_ERR_CUDA, std::string("key expansion: ") + cudaGetErrorString(e));
+    return make_error(B2BFS_ERR_RANGE, "edge list holds a vertex id outside [0, vertex_num)");
+  }
+  return build_csr_from_keys(ka, N, n, 0, n, ks, dedup, directed, 0, stream, out, launches);
+}
+
+// keys of this rank's rows (row id relative to row_begin in the top bits) -> CSR.  Takes ownership of
+// `ka` (freed on every path).
+Status build_csr_from_keys(uint64_t* ka, int64_t N, int64_t n, int64_t row_begin, int64_t row_end, const KeySpec& ks, int dedup,
+                           int directed, int64_t nwords_override, cudaStream_t stream, BuiltCsr* out, int64_t* launches) {
   *out = BuiltCsr();
   const int64_t nrows = row_end - row_begin;
-  const int vbits = bits_for(n);
+  const int vbits = ks.vbits, rshift = ks.rshift;
   const int rbits = bits_for(nrows > 0 ? nrows : 1);
-  if (directed && partitioned) return make_error(B2BFS_ERR_UNSUPPORTED, "directed graphs are not partitioned across GPUs");
-  const int cbits = (hub_first && !directed && vbits + rbits + 4 <= 64) ? 4 : 0;
-  const int rshift = vbits + cbits;
   const int64_t nwords = nwords_override > 0 ? nwords_override : ((nrows + 31) / 32 + 3) / 4 * 4;
   out->nrows = nrows;
   out->nwords = nwords;
+  (void)n;
 
-  unsigned long long* counters = nullptr;  // [0] append cursor / owned total, [1] wide items, [2] max degree
-  int* bad = nullptr;
   DeviceTemps temps;
+  temps.ptrs[temps.count++] = ka;
+  unsigned long long* counters = nullptr;  // [1] wide items, [2] max degree
   B2_CUDA(temps.alloc(&counters, 4 * sizeof(unsigned long long)));
-  B2_CUDA(temps.alloc(&bad, sizeof(int)));
   B2_CUDA(cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), stream));
-  B2_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), stream));
 
-  const int64_t eblocks = (m + kBlock - 1) / kBlock;
-  const int egrid = (int)(eblocks < (int64_t)kSMs * 16 ? (eblocks > 0 ? eblocks : 1) : (int64_t)kSMs * 16);
-  int64_t N = directed ? m : 2 * m;
-  if (partitioned) {
-    count_owned_kernel<<<egrid, kBlock, 0, stream>>>(src, dst, m, row_begin, row_end, counters);
-    unsigned long long owned = 0;
-    B2_CUDA(cudaMemcpyAsync(&owned, counters, sizeof(owned), cudaMemcpyDeviceToHost, stream));
-    B2_CUDA(cudaStreamSynchronize(stream));
-    B2_CUDA(cudaMemsetAsync(counters, 0, sizeof(unsigned long long), stream));
-    N = (int64_t)owned;
-    if (launches) *launches += 1;
-  }
-
-  uint64_t *ka = nullptr, *kb = nullptr, *sorted = nullptr;
+  uint64_t *kb = nullptr, *sorted = nullptr;
   void* scratch = nullptr;
-  const size_t kbytes = (size_t)(N > 0 ? N : 1) * sizeof(uint64_t);
-  B2_CUDA(temps.alloc(&ka, kbytes));
-  B2_CUDA(temps.alloc(&kb, kbytes));
+  B2_CUDA(temps.alloc(&kb, (size_t)(N > 0 ? N : 1) * sizeof(uint64_t)));
   const int G = sort_grid_size(N);
   B2_CUDA(temps.alloc(&scratch, sort_scratch_bytes(N) + (size_t)(G + 1) * sizeof(uint64_t)));
-
-  uint32_t* degc = nullptr;
-  if (cbits) {
-    B2_CUDA(temps.alloc(&degc, (size_t)n * sizeof(uint32_t)));
-    B2_CUDA(cudaMemsetAsync(degc, 0, (size_t)n * sizeof(uint32_t), stream));
-    degree_count_kernel<<<egrid, kBlock, 0, stream>>>(src, dst, m, n, degc);
-    if (launches) *launches += 1;
-  }
-  expand_edges_kernel<<<egrid, kBlock, 0, stream>>>(src, dst, m, n, vbits, rshift, degc, row_begin, row_end, ka,
-                                                    partitioned ? counters : nullptr, bad, directed);
-  if (launches) *launches += 1;
-  int bad_h = 0;
-  B2_CUDA(cudaMemcpyAsync(&bad_h, bad, sizeof(int), cudaMemcpyDeviceToHost, stream));
-  B2_CUDA(cudaStreamSynchronize(stream));
-  if (bad_h) {
-    return make_error(B2BFS_ERR_RANGE, "edge list holds a vertex id outside [0, vertex_num)");
-  }
 
   B2_TRY(radix_sort_u64(ka, kb, N, rshift + rbits, scratch, stream, &sorted, launches));
 
