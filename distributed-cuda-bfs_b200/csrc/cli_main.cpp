@@ -92,10 +92,16 @@ static int launch_ranks(int argc, char** argv, int world) {
   snprintf(id_file, sizeof(id_file), "/tmp/b2bfs_id_%d", (int)getpid());
   unlink(id_file);
   std::vector<pid_t> kids;
+  fflush(stdout);
   for (int r = 0; r < world; ++r) {
     const pid_t pid = fork();  // before this process has touched CUDA
     if (pid < 0) { perror("b2bfs: fork"); break; }
-    if (pid == 0) _exit(run_rank(argc, argv, r, world, id_file));
+    if (pid == 0) {
+      const int rc = run_rank(argc, argv, r, world, id_file);
+      fflush(stdout);
+      fflush(stderr);
+      _exit(rc);
+    }
     kids.push_back(pid);
   }
   int worst = (int)kids.size() == world ? 0 : 1;
