@@ -39,6 +39,8 @@ struct b2bfs {
   SearchView sv{};
   Control* pinned_ctl = nullptr;
   int grid = 0;
+  int grid_cluster = 0;  // grid of the search kernel when launched in clusters (0: not possible here)
+  int use_cluster = 1;
   int64_t build_launches = 0;
   // multi-rank (world > 1): 1-D partition of the rows, NCCL communicator, exchange buffers
   MultiContext mc;
@@ -360,6 +362,7 @@ static BfsParams make_params(const b2bfs* h) {
   p.tn.beta = h->beta;
   p.tn.gamma = h->gamma;
   p.tn.huge_min = h->huge_min;
+  p.tn.cluster = (h->world == 1 && h->use_cluster && h->grid_cluster > 0) ? 1 : 0;
   p.tn.xfullpush = h->xfullpush;
   return p;
 }
@@ -479,6 +482,7 @@ int b2bfs_create(b2bfs_t** out, int device) {
     API_CUDA(nullptr, cudaEventCreate(&h->ev1));
     API_CUDA(nullptr, cudaMallocHost(&h->pinned_ctl, sizeof(Control)));
     Status s = search_grid_size(device, &h->grid);
+    if (s.ok()) s = search_cluster_grid_size(h->grid, &h->grid_cluster);
     return s.ok() ? B2BFS_OK : fail(nullptr, s);
   };
   const int rc = create();
@@ -566,6 +570,7 @@ int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value) {
   else if (k == "beta" && value >= 1 && value <= (1 << 20)) h->beta = (int)value;
   else if (k == "gamma" && value >= 0 && value <= (1 << 20)) h->gamma = (int)value;
   else if (k == "xfullpush" && (value == 0 || value == 1)) h->xfullpush = (int)value;
+  else if (k == "cluster" && (value == 0 || value == 1)) h->use_cluster = (int)value;
   else if (k == "huge_min" && (value == 0 || (value >= 2 * kCtaChunk && value <= (1 << 30)))) h->huge_min = (int)value;
   else return fail(h, B2BFS_ERR_ARG, "unknown option or value out of range: " + k);
   return B2BFS_OK;
@@ -585,6 +590,8 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   else if (k == "gamma") *value = h->gamma;
   else if (k == "xfullpush") *value = h->xfullpush;
   else if (k == "huge_min") *value = h->huge_min;
+  else if (k == "cluster") *value = (h->world == 1 && h->use_cluster && h->grid_cluster > 0) ? 1 : 0;
+  else if (k == "grid_cluster") *value = h->grid_cluster;
   else if (k == "grid") *value = h->grid;
   else if (k == "gather_parent") *value = h->gather_parent;
   else if (k == "multi_engine") *value = (h->world > 1 && h->p2p_ready && h->multi_engine == 0) ? 0 : 1;
@@ -782,7 +789,7 @@ static int run_impl(b2bfs_t* h, int64_t src, int32_t* depth_out, int32_t* parent
                                                  reinterpret_cast<int*>(h->cmp_scratch), &launches))
            : p2p ? run_fused_multi(p, src, h->grid_multi, h->stream, &mr.launches)
            : multi ? run_multi(p, h->mc, src, h->grid, h->stream, &mr)
-           : (h->engine == B2BFS_ENGINE_FUSED) ? run_fused(p, src, h->grid, h->stream, &launches)
+           : (h->engine == B2BFS_ENGINE_FUSED) ? run_fused(p, src, p.tn.cluster ? h->grid_cluster : h->grid, h->stream, &launches)
                                                : run_stepwise(p, src, h->grid, h->stream, h->pinned_ctl, &launches);
   if (!s.ok()) return fail(h, s);
   API_CUDA(h, cudaEventRecord(h->ev1, h->stream));

@@ -1026,6 +1026,154 @@ __device__ __forceinline__ void trace_mark(Control* c, int& n, int level, int ph
   if (blockIdx.x == 0 && threadIdx.x == 0) trace_put(c, level, phase);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Cluster mode - high-diameter graphs (grids, road networks: thousands of levels of a few thousand
+// vertices each).  What such a level costs is its chain of dependent memory round trips, and on the
+// global-memory path most links of that chain are bookkeeping: the queue read, the tail atomic, the
+// barrier's arrival atomic and spin, the counter reads.  Here the first cluster of the grid keeps the
+// frontier in its CTAs' SHARED memory (a discovery is appended to the queue of the CTA its id hashes
+// to, through distributed shared memory), the level barrier is the hardware cluster barrier, and the
+// counters every CTA needs for the level decision are read from the other CTAs' shared memory.  What
+// is left of the chain: row extent -> neighbour ids -> the claim's atomicOr.
+// Only frontiers of narrow rows qualify (no vertex of kNarrow or more entries).  On leaving, the
+// frontier is handed back through the ordinary work lists, routed by degree.
+// Replaces, per level, the reference's launch + cudaDeviceSynchronize + peer copies + managed-counter
+// round trips (bfs.cu:569-619).
+// ---------------------------------------------------------------------------------------------
+constexpr int kClusterQCap = 3072;                     // per CTA and queue
+constexpr unsigned kClusterMaxQ = kClusterBlocks * kClusterQCap / 2;   // leave above this many frontier vertices
+constexpr unsigned kClusterMaxEdges = 1u << 16;        // ... or frontier entries
+constexpr unsigned kClusterEnterQ = 4096, kClusterEnterEdges = 1u << 15;
+struct ClusterQ {
+  int32_t q[2][kClusterQCap];
+  unsigned int cnt[2], edges[2], wide[2];
+  unsigned int base;  // scratch for the dump
+};
+static_assert(sizeof(ClusterQ) <= sizeof(WarpStage) * kWarpsPerBlock, "the cluster queues overlay the staging buffers");
+
+__device__ __forceinline__ bool cluster_eligible(const BfsParams& p, const LoopState& st, unsigned hubs) {
+  return p.tn.cluster && st.mode == 0 && st.cur_wide == 0 && hubs == 0 && st.cur_q <= kClusterEnterQ &&
+         st.frontier_edges <= kClusterEnterEdges;
+}
+
+// run by the CTAs of cluster 0; returns what the level that follows needs (st, conversion); the
+// frontier of level st.level is back in the global work lists, slot counters set
+__device__ __noinline__ Conversion cluster_levels(const BfsParams& p, LoopState& st, WarpStage* stage) {
+  cg::cluster_group cluster = cg::this_cluster();
+  ClusterQ* cq = reinterpret_cast<ClusterQ*>(stage);
+  const unsigned c = cluster.block_rank(), nc = cluster.num_blocks();
+  const unsigned t = threadIdx.x, lane = t & 31;
+  Control* ctl = p.s.ctl;
+  if (t == 0) {
+    cq->cnt[0] = st.cur_q > c ? (st.cur_q - c + nc - 1) / nc : 0u;
+    cq->cnt[1] = 0;
+    cq->edges[0] = cq->edges[1] = cq->wide[0] = cq->wide[1] = 0;
+    if (c == 0) { ctl->dump_count = 0; ctl->cluster_overflow = 0; }
+  }
+  {  // the frontier, dealt round-robin to the CTAs
+    const int32_t* gq = p.s.queue[st.level & 1];
+    for (unsigned j = t; c + nc * j < st.cur_q; j += kBlock) cq->q[0][j] = __ldcg(gq + c + nc * j);
+  }
+  __threadfence();
+  __syncthreads();
+  int cur = 0;
+  bool first = true;
+  Conversion cv = kNoConversion;
+  for (;;) {
+    // ---- A: extents of my part of the frontier (degree sum, any wide row?)
+    const unsigned cnt = cq->cnt[cur];
+    unsigned my_edges = 0, my_wide = 0;
+    for (unsigned j = t; j < cnt; j += kBlock) {
+      const int32_t u = cq->q[cur][j];
+      const unsigned d = (unsigned)(__ldg(p.g.rowptr + u + 1) - __ldg(p.g.rowptr + u));
+      my_edges += d;
+      my_wide |= d >= (unsigned)kNarrow;
+    }
+    for (int o = 16; o; o >>= 1) {
+      my_edges += __shfl_xor_sync(0xffffffffu, my_edges, o);
+      my_wide |= __shfl_xor_sync(0xffffffffu, my_wide, o);
+    }
+    if (lane == 0 && my_edges) atomicAdd(&cq->edges[cur], my_edges);
+    if (lane == 0 && my_wide) atomicOr(&cq->wide[cur], 1u);
+    cluster.sync();  // (1) every CTA's count, degree sum and flag for this level are final
+    unsigned nq_t = 0, mf_t = 0, wide_t = 0;
+    for (unsigned r = 0; r < nc; ++r) {
+      const ClusterQ* o = cluster.map_shared_rank(cq, r);
+      nq_t += o->cnt[cur];
+      mf_t += o->edges[cur];
+      wide_t |= o->wide[cur];
+    }
+    if (!first) cv = advance(st, p.tn, p.g.n, nq_t, 0, 0, mf_t);  // closes the previous level: this queue is what it found
+    first = false;
+    const bool overflow = *reinterpret_cast<volatile unsigned int*>(&ctl->cluster_overflow) != 0;
+    if (st.done || cv != kNoConversion || wide_t || overflow || nq_t > kClusterMaxQ || mf_t > kClusterMaxEdges) break;
+    // ---- B: expand
+    const int nxt = cur ^ 1;
+    if (t == 0) { cq->edges[nxt] = 0; cq->wide[nxt] = 0; }  // last read before barrier (2) of the previous level
+    const int level = st.level;
+    for (unsigned j = t; j < cnt; j += kBlock) {
+      const int32_t u = cq->q[cur][j];
+      const int64_t rs = __ldg(p.g.rowptr + u), re = __ldg(p.g.rowptr + u + 1);
+      for (int64_t e = rs; e < re; ++e) {
+        const int32_t v = __ldg(p.g.col + e);
+        const uint32_t bit = 1u << (v & 31);
+        if (atomicOr(&p.s.visited[(uint32_t)v >> 5], bit) & bit) continue;
+        p.s.depth[v] = level + 1;
+        p.s.parent[v] = u;
+        ClusterQ* o = cluster.map_shared_rank(cq, ((uint32_t)v ^ ((uint32_t)v >> 9)) % nc);
+        const unsigned pos = atomicAdd(&o->cnt[nxt], 1u);
+        if (pos < (unsigned)kClusterQCap) {
+          o->q[nxt][pos] = v;
+        } else {  // that queue is full: the vertex goes to the global list, the mode ends at the next level
+          atomicSub(&o->cnt[nxt], 1u);
+          p.s.queue[(level + 2) & 1][atomicAdd(&ctl->dump_count, 1u)] = v;
+          atomicExch(&ctl->cluster_overflow, 1u);
+        }
+      }
+    }
+    cluster.sync();  // (2) every append has landed
+    if (t == 0) cq->cnt[cur] = 0;  // becomes the next level's `nxt`: nobody appends before barrier (1)
+    cur = nxt;
+  }
+  if (st.done) return cv;
+  // ---- leave: my part of the frontier -> the global list behind the spills, then all of it -> the
+  // ordinary work lists of level st.level, routed by degree
+  int32_t* tmp = p.s.queue[(st.level + 1) & 1];
+  const unsigned cnt = cq->cnt[cur];
+  if (t == 0) {
+    cq->base = atomicAdd(&ctl->dump_count, cnt);
+    if (c == 0) {
+      for (int k = 0; k < 2; ++k) {
+        LevelSlot* z = &ctl->slot[(st.level + k) & 3];
+        z->q_count = 0; z->wide_count = 0; z->huge_count = 0; z->edges = 0; z->bu_count = 0; z->bu_cursor = 0;
+      }
+    }
+  }
+  __syncthreads();
+  for (unsigned j = t; j < cnt; j += kBlock) tmp[cq->base + j] = cq->q[cur][j];
+  __threadfence();
+  cluster.sync();  // the list is complete; the queues in shared memory are no longer needed
+  const unsigned total = *reinterpret_cast<volatile unsigned int*>(&ctl->dump_count);
+  {
+    LevelSlot* cs = &ctl->slot[st.level & 3];
+    const HubOut hub = hub_out(p, st.level);
+    WarpStage& sg = stage[t >> 5];
+    if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
+    __syncwarp();
+    const unsigned stride = nc * kBlock;
+    for (unsigned i0 = 0; i0 < total; i0 += stride) {  // warp-uniform trip count
+      const unsigned i = i0 + c * kBlock + t;
+      if (i < total) {
+        const int32_t v = __ldcg(tmp + i);
+        route_vertex(sg, v, __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v), hub);
+      }
+      stage_flush(sg, cs, p.s.queue[st.level & 1], p.s.wideq[st.level & 1], false);
+    }
+    stage_flush(sg, cs, p.s.queue[st.level & 1], p.s.wideq[st.level & 1], true);
+  }
+  return cv;
+}
+
 // work items of the current frontier that only a full grid should take on: hub-row items
 __device__ __forceinline__ unsigned hub_items(const BfsParams& p, int level) {
   return p.s.hugeq[0] ? ld_volatile(&p.s.ctl->slot[level & 3].huge_count) : 0u;
@@ -1050,7 +1198,37 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
   while (!st.done) {
     Conversion cv = kNoConversion;
     bool marked = false;
-    if (st.mode == 0 && frontier_work(st) <= kGroupMaxWork && hub_items(p, st.level) == 0) {
+    const unsigned hubs = hub_items(p, st.level);
+    if (cluster_eligible(p, st, hubs)) {
+      ++group_seq;
+      if ((int)blockIdx.x < kClusterBlocks) {
+        cv = cluster_levels(p, st, stage);
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+          p.s.ctl->resume_state = st;
+          p.s.ctl->resume_conversion = (int)cv;
+          __threadfence();
+          *reinterpret_cast<volatile unsigned int*>(&p.s.ctl->group_exit_seq) = group_seq;
+        }
+      } else {
+        if (threadIdx.x == 0)
+          while (ld_volatile(&p.s.ctl->group_exit_seq) < group_seq) __nanosleep(2000);
+        __syncthreads();
+      }
+      grid.sync();
+      if ((int)blockIdx.x >= kClusterBlocks) {  // catch up with what the cluster decided
+        const volatile LoopState* rs = &p.s.ctl->resume_state;
+        st.level = rs->level; st.mode = rs->mode; st.fb = rs->fb; st.done = rs->done;
+        st.prev_nf = rs->prev_nf; st.unexplored = rs->unexplored; st.td_levels = rs->td_levels;
+        st.bu_levels = rs->bu_levels; st.frontier_edges = rs->frontier_edges;
+        cv = (Conversion)(*reinterpret_cast<const volatile int*>(&p.s.ctl->resume_conversion));
+      }
+      if (!st.done) {  // the frontier came back through the work lists, routed by degree
+        const LevelSlot* cs = &p.s.ctl->slot[st.level & 3];
+        st.cur_q = ld_volatile(&cs->q_count);
+        st.cur_wide = ld_volatile(&cs->wide_count);
+      }
+      trace_mark(p.s.ctl, ntrace, st.level, 7);
+    } else if (st.mode == 0 && frontier_work(st) <= kGroupMaxWork && hubs == 0) {
       ++group_seq;
       if ((int)blockIdx.x < group) {
         do {
@@ -1402,8 +1580,50 @@ Status run_fused(const BfsParams& p, int64_t src, int grid, cudaStream_t stream,
   BfsParams pp = p;
   int64_t s = src;
   void* args[] = {&pp, &s};
-  B2_CUDA(cudaLaunchCooperativeKernel((const void*)bfs_fused_kernel, dim3(grid), dim3(kBlock), args, 0, stream));
+  if (p.tn.cluster) {  // cooperative AND in clusters of kClusterBlocks CTAs (grid is a multiple of it)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kBlock);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = kClusterBlocks;
+    attr[1].val.clusterDim.y = 1;
+    attr[1].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 2;
+    B2_CUDA(cudaLaunchKernelExC(&cfg, (const void*)bfs_fused_kernel, args));
+  } else {
+    B2_CUDA(cudaLaunchCooperativeKernel((const void*)bfs_fused_kernel, dim3(grid), dim3(kBlock), args, 0, stream));
+  }
   if (launches) *launches += 1;
+  return Status();
+}
+
+// Largest grid of the search kernel that is co-resident when launched in clusters, 0 if the device
+// (or this driver) cannot run it that way or would lose more than a tenth of the plain grid.
+Status search_cluster_grid_size(int plain_grid, int* grid_out) {
+  *grid_out = 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(plain_grid / kClusterBlocks * kClusterBlocks);
+  cfg.blockDim = dim3(kBlock);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kClusterBlocks;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int clusters = 0;
+  if (cudaOccupancyMaxActiveClusters(&clusters, (const void*)bfs_fused_kernel, &cfg) != cudaSuccess) {
+    cudaGetLastError();
+    return Status();
+  }
+  int g = clusters * kClusterBlocks;
+  if (g > plain_grid / kClusterBlocks * kClusterBlocks) g = plain_grid / kClusterBlocks * kClusterBlocks;
+  if (g * 10 >= plain_grid * 9) *grid_out = g;
   return Status();
 }
 

@@ -160,6 +160,7 @@ int b2bfs_search_noalloc(int device, int64_t n, int64_t entries, const int64_t* 
   p.tn.alpha = 14;
   p.tn.beta = 24;
   p.tn.gamma = 0;
+  p.tn.cluster = 0;
   p.tn.huge_min = 0;  // no hub-item lists in the built-in scratch: hub rows stay warp items
   p.tn.xfullpush = 0;
 
