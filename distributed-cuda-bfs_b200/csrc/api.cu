@@ -41,6 +41,7 @@ struct b2bfs {
   int grid = 0;
   int grid_cluster = 0;  // grid of the search kernel when launched in clusters (0: not possible here)
   int use_cluster = 1;
+  bool has_graph_rows_narrow() const { return has_graph && csr.max_degree < kNarrow; }
   int64_t build_launches = 0;
   // multi-rank (world > 1): 1-D partition of the rows, NCCL communicator, exchange buffers
   MultiContext mc;
@@ -362,7 +363,8 @@ static BfsParams make_params(const b2bfs* h) {
   p.tn.beta = h->beta;
   p.tn.gamma = h->gamma;
   p.tn.huge_min = h->huge_min;
-  p.tn.cluster = (h->world == 1 && h->use_cluster && h->grid_cluster > 0) ? 1 : 0;
+  // graphs of narrow rows only (grids, road-like meshes): the kernel instance with the cluster mode
+  p.tn.cluster = (h->world == 1 && h->use_cluster && h->grid_cluster > 0 && h->has_graph_rows_narrow()) ? 1 : 0;
   p.tn.xfullpush = h->xfullpush;
   return p;
 }
@@ -590,7 +592,7 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   else if (k == "gamma") *value = h->gamma;
   else if (k == "xfullpush") *value = h->xfullpush;
   else if (k == "huge_min") *value = h->huge_min;
-  else if (k == "cluster") *value = (h->world == 1 && h->use_cluster && h->grid_cluster > 0) ? 1 : 0;
+  else if (k == "cluster") *value = (h->world == 1 && h->use_cluster && h->grid_cluster > 0 && h->has_graph_rows_narrow()) ? 1 : 0;
   else if (k == "grid_cluster") *value = h->grid_cluster;
   else if (k == "grid") *value = h->grid;
   else if (k == "gather_parent") *value = h->gather_parent;

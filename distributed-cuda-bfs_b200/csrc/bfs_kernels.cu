@@ -1040,34 +1040,35 @@ __device__ __forceinline__ void trace_mark(Control* c, int& n, int level, int ph
 // Replaces, per level, the reference's launch + cudaDeviceSynchronize + peer copies + managed-counter
 // round trips (bfs.cu:569-619).
 // ---------------------------------------------------------------------------------------------
-constexpr int kClusterQCap = 3072;                     // per CTA and queue
+constexpr int kClusterQCap = 2048;                     // per CTA and queue; three queues (ring indexed by level % 3)
 constexpr unsigned kClusterMaxQ = kClusterBlocks * kClusterQCap / 2;   // leave above this many frontier vertices
-constexpr unsigned kClusterMaxEdges = 1u << 16;        // ... or frontier entries
-constexpr unsigned kClusterEnterQ = 4096, kClusterEnterEdges = 1u << 15;
+constexpr unsigned kClusterEnterQ = 4096;
 struct ClusterQ {
-  int32_t q[2][kClusterQCap];
-  unsigned int cnt[2], edges[2], wide[2];
+  int32_t q[3][kClusterQCap];
+  unsigned int cnt[3], edges[3];
   unsigned int base;  // scratch for the dump
 };
 static_assert(sizeof(ClusterQ) <= sizeof(WarpStage) * kWarpsPerBlock, "the cluster queues overlay the staging buffers");
 
-__device__ __forceinline__ bool cluster_eligible(const BfsParams& p, const LoopState& st, unsigned hubs) {
-  return p.tn.cluster && st.mode == 0 && st.cur_wide == 0 && hubs == 0 && st.cur_q <= kClusterEnterQ &&
-         st.frontier_edges <= kClusterEnterEdges;
+// The cluster variant of the kernel is chosen per GRAPH (api.cu): only graphs without a single row of
+// kNarrow or more entries (grids, road-like meshes) get it, so a frontier here never holds a wide row.
+__device__ __forceinline__ bool cluster_eligible(const LoopState& st) {
+  return st.mode == 0 && st.cur_wide == 0 && st.cur_q <= kClusterEnterQ;
 }
 
-// run by the CTAs of cluster 0; returns what the level that follows needs (st, conversion); the
-// frontier of level st.level is back in the global work lists, slot counters set
-__device__ __noinline__ Conversion cluster_levels(const BfsParams& p, LoopState& st, WarpStage* stage) {
+// run by the CTAs of cluster 0; on return st describes the level that follows; unless st.done the
+// frontier of level st.level is back in the global work lists with its slot counters set
+__device__ __forceinline__ Conversion cluster_levels(const BfsParams& p, LoopState& st, WarpStage* stage) {
   cg::cluster_group cluster = cg::this_cluster();
   ClusterQ* cq = reinterpret_cast<ClusterQ*>(stage);
   const unsigned c = cluster.block_rank(), nc = cluster.num_blocks();
   const unsigned t = threadIdx.x, lane = t & 31;
   Control* ctl = p.s.ctl;
+  unsigned cur = 0;  // ring position of the current frontier's queue
   if (t == 0) {
     cq->cnt[0] = st.cur_q > c ? (st.cur_q - c + nc - 1) / nc : 0u;
-    cq->cnt[1] = 0;
-    cq->edges[0] = cq->edges[1] = cq->wide[0] = cq->wide[1] = 0;
+    cq->cnt[1] = cq->cnt[2] = 0;
+    cq->edges[0] = cq->edges[1] = cq->edges[2] = 0;
     if (c == 0) { ctl->dump_count = 0; ctl->cluster_overflow = 0; }
   }
   {  // the frontier, dealt round-robin to the CTAs
@@ -1075,69 +1076,77 @@ __device__ __noinline__ Conversion cluster_levels(const BfsParams& p, LoopState&
     for (unsigned j = t; c + nc * j < st.cur_q; j += kBlock) cq->q[0][j] = __ldcg(gq + c + nc * j);
   }
   __threadfence();
-  __syncthreads();
-  int cur = 0;
-  bool first = true;
+  cluster.sync();
   Conversion cv = kNoConversion;
   for (;;) {
-    // ---- A: extents of my part of the frontier (degree sum, any wide row?)
+    const unsigned nxt = cur == 2 ? 0 : cur + 1, spare = nxt == 2 ? 0 : nxt + 1;
     const unsigned cnt = cq->cnt[cur];
-    unsigned my_edges = 0, my_wide = 0;
-    for (unsigned j = t; j < cnt; j += kBlock) {
-      const int32_t u = cq->q[cur][j];
-      const unsigned d = (unsigned)(__ldg(p.g.rowptr + u + 1) - __ldg(p.g.rowptr + u));
-      my_edges += d;
-      my_wide |= d >= (unsigned)kNarrow;
-    }
-    for (int o = 16; o; o >>= 1) {
-      my_edges += __shfl_xor_sync(0xffffffffu, my_edges, o);
-      my_wide |= __shfl_xor_sync(0xffffffffu, my_wide, o);
-    }
-    if (lane == 0 && my_edges) atomicAdd(&cq->edges[cur], my_edges);
-    if (lane == 0 && my_wide) atomicOr(&cq->wide[cur], 1u);
-    cluster.sync();  // (1) every CTA's count, degree sum and flag for this level are final
-    unsigned nq_t = 0, mf_t = 0, wide_t = 0;
-    for (unsigned r = 0; r < nc; ++r) {
-      const ClusterQ* o = cluster.map_shared_rank(cq, r);
-      nq_t += o->cnt[cur];
-      mf_t += o->edges[cur];
-      wide_t |= o->wide[cur];
-    }
-    if (!first) cv = advance(st, p.tn, p.g.n, nq_t, 0, 0, mf_t);  // closes the previous level: this queue is what it found
-    first = false;
-    const bool overflow = *reinterpret_cast<volatile unsigned int*>(&ctl->cluster_overflow) != 0;
-    if (st.done || cv != kNoConversion || wide_t || overflow || nq_t > kClusterMaxQ || mf_t > kClusterMaxEdges) break;
-    // ---- B: expand
-    const int nxt = cur ^ 1;
-    if (t == 0) { cq->edges[nxt] = 0; cq->wide[nxt] = 0; }  // last read before barrier (2) of the previous level
     const int level = st.level;
+    // recycle the ring: the count that collects the level after next, the degree sum of the next level
+    // (both were last read before the previous barrier, by CTAs that have all passed it since)
+    if (t == 0) { cq->cnt[spare] = 0; cq->edges[nxt] = 0; }
+    unsigned my_edges = 0;
     for (unsigned j = t; j < cnt; j += kBlock) {
       const int32_t u = cq->q[cur][j];
       const int64_t rs = __ldg(p.g.rowptr + u), re = __ldg(p.g.rowptr + u + 1);
-      for (int64_t e = rs; e < re; ++e) {
-        const int32_t v = __ldg(p.g.col + e);
-        const uint32_t bit = 1u << (v & 31);
-        if (atomicOr(&p.s.visited[(uint32_t)v >> 5], bit) & bit) continue;
-        p.s.depth[v] = level + 1;
-        p.s.parent[v] = u;
-        ClusterQ* o = cluster.map_shared_rank(cq, ((uint32_t)v ^ ((uint32_t)v >> 9)) % nc);
-        const unsigned pos = atomicAdd(&o->cnt[nxt], 1u);
-        if (pos < (unsigned)kClusterQCap) {
-          o->q[nxt][pos] = v;
-        } else {  // that queue is full: the vertex goes to the global list, the mode ends at the next level
-          atomicSub(&o->cnt[nxt], 1u);
-          p.s.queue[(level + 2) & 1][atomicAdd(&ctl->dump_count, 1u)] = v;
-          atomicExch(&ctl->cluster_overflow, 1u);
+      my_edges += (unsigned)(re - rs);
+      for (int64_t e0 = rs; e0 < re; e0 += 4) {  // four neighbours at a time: loads, claims and appends each in flight together
+        int32_t v[4];
+        uint32_t old[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = e0 + k < re ? __ldg(p.g.col + e0 + k) : -1;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          old[k] = v[k] >= 0 ? atomicOr(&p.s.visited[(uint32_t)v[k] >> 5], 1u << (v[k] & 31)) : 0xffffffffu;
+        ClusterQ* o[4];
+        unsigned pos[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          pos[k] = 0xffffffffu;
+          if (v[k] >= 0 && !((old[k] >> (v[k] & 31)) & 1u)) {
+            p.s.depth[v[k]] = level + 1;
+            p.s.parent[v[k]] = u;
+            o[k] = cluster.map_shared_rank(cq, ((uint32_t)v[k] ^ ((uint32_t)v[k] >> 9)) % nc);
+            pos[k] = atomicAdd(&o[k]->cnt[nxt], 1u);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (pos[k] == 0xffffffffu) continue;
+          if (pos[k] < (unsigned)kClusterQCap) {
+            o[k]->q[nxt][pos[k]] = v[k];
+          } else {  // that queue is full: the vertex goes to the global list, the mode ends after this level
+            atomicSub(&o[k]->cnt[nxt], 1u);
+            p.s.queue[level & 1][atomicAdd(&ctl->dump_count, 1u)] = v[k];
+            atomicExch(&ctl->cluster_overflow, 1u);
+          }
         }
       }
     }
-    cluster.sync();  // (2) every append has landed
-    if (t == 0) cq->cnt[cur] = 0;  // becomes the next level's `nxt`: nobody appends before barrier (1)
+    for (int o2 = 16; o2; o2 >>= 1) my_edges += __shfl_xor_sync(0xffffffffu, my_edges, o2);
+    if (lane == 0 && my_edges) atomicAdd(&cq->edges[cur], my_edges);
+    cluster.sync();  // every append has landed, every count and degree sum is final
+    unsigned nq_t = 0, mf_cur = 0;
+    const unsigned cur_t = st.cur_q;  // what the previous level (or the entry) counted
+#pragma unroll
+    for (unsigned r = 0; r < (unsigned)kClusterBlocks; ++r) {
+      if (r < nc) {
+        const ClusterQ* oq = cluster.map_shared_rank(cq, r);
+        nq_t += oq->cnt[nxt];
+        mf_cur += oq->edges[cur];
+      }
+    }
+    // the degree sum of the NEW frontier is not known yet (its rows are read next level): the mean
+    // degree of the level just expanded stands in for it - it only feeds the switch heuristic
+    const unsigned long long mf_est = (unsigned long long)nq_t * (cur_t ? (mf_cur + cur_t - 1) / cur_t : 1u);
+    cv = advance(st, p.tn, p.g.n, nq_t, 0, 0, mf_est);
     cur = nxt;
+    const bool overflow = *reinterpret_cast<volatile unsigned int*>(&ctl->cluster_overflow) != 0;
+    if (st.done || cv != kNoConversion || overflow || nq_t > kClusterMaxQ) break;
   }
   if (st.done) return cv;
   // ---- leave: my part of the frontier -> the global list behind the spills, then all of it -> the
-  // ordinary work lists of level st.level, routed by degree
+  // ordinary work lists of level st.level
   int32_t* tmp = p.s.queue[(st.level + 1) & 1];
   const unsigned cnt = cq->cnt[cur];
   if (t == 0) {
@@ -1179,7 +1188,8 @@ __device__ __forceinline__ unsigned hub_items(const BfsParams& p, int level) {
   return p.s.hugeq[0] ? ld_volatile(&p.s.ctl->slot[level & 3].huge_count) : 0u;
 }
 
-__global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(BfsParams p, int64_t src) {
+template <bool kCluster>
+__device__ __forceinline__ void fused_search(BfsParams& p, int64_t src) {
   __shared__ WarpStage stage[kWarpsPerBlock];
   __shared__ HubStage hub;
   if (threadIdx.x == 0) hub_stage_init(&hub);
@@ -1199,7 +1209,7 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
     Conversion cv = kNoConversion;
     bool marked = false;
     const unsigned hubs = hub_items(p, st.level);
-    if (cluster_eligible(p, st, hubs)) {
+    if (kCluster && cluster_eligible(st)) {
       ++group_seq;
       if ((int)blockIdx.x < kClusterBlocks) {
         cv = cluster_levels(p, st, stage);
@@ -1297,6 +1307,17 @@ __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(
     p.s.ctl->result.td_levels = st.td_levels;
     p.s.ctl->result.bu_levels = st.bu_levels;
   }
+}
+
+// two instances of the search: the plain one, and one that also holds the cluster mode (chosen per
+// graph by the host: only graphs whose every row is narrower than kNarrow run it, launched in
+// clusters of kClusterBlocks CTAs).  Separate instances keep the extra code's register pressure
+// away from the power-law path.
+__global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(BfsParams p, int64_t src) {
+  fused_search<false>(p, src);
+}
+__global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_cluster_kernel(BfsParams p, int64_t src) {
+  fused_search<true>(p, src);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1594,7 +1615,7 @@ Status run_fused(const BfsParams& p, int64_t src, int grid, cudaStream_t stream,
     attr[1].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 2;
-    B2_CUDA(cudaLaunchKernelExC(&cfg, (const void*)bfs_fused_kernel, args));
+    B2_CUDA(cudaLaunchKernelExC(&cfg, (const void*)bfs_fused_cluster_kernel, args));
   } else {
     B2_CUDA(cudaLaunchCooperativeKernel((const void*)bfs_fused_kernel, dim3(grid), dim3(kBlock), args, 0, stream));
   }
@@ -1617,7 +1638,7 @@ Status search_cluster_grid_size(int plain_grid, int* grid_out) {
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   int clusters = 0;
-  if (cudaOccupancyMaxActiveClusters(&clusters, (const void*)bfs_fused_kernel, &cfg) != cudaSuccess) {
+  if (cudaOccupancyMaxActiveClusters(&clusters, (const void*)bfs_fused_cluster_kernel, &cfg) != cudaSuccess) {
     cudaGetLastError();
     return Status();
   }

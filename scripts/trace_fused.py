@@ -10,7 +10,7 @@ for a in sys.argv[4:]:
 h.generate(kind, scale, 16, 1)
 rowptr, _ = h.csr(); deg = np.diff(rowptr)
 roots = np.random.default_rng(2).choice(np.flatnonzero(deg > 0), nroots + 2, replace=False)
-names = {-1: "start", 0: "reset", 1: "td", 2: "bu", 3: "q2b", 4: "b2q", 5: "grp", 6: "claim"}
+names = {-1: "start", 0: "reset", 1: "td", 2: "bu", 3: "q2b", 4: "b2q", 5: "grp", 6: "claim", 7: "cluster"}
 for r in roots:
     st = h.run_device(int(r))
     tr = h.last_trace()
