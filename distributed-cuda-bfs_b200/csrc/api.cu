@@ -39,7 +39,7 @@ struct b2bfs {
   SearchView sv{};
   Control* pinned_ctl = nullptr;
   int grid = 0;
-  int grid_cluster = 0;  // grid of the search kernel when launched in clusters (0: not possible here)
+  int grid_cluster = 0, cluster_size = 0;  // grid and CTAs per cluster of the cluster-mode kernel (0: not possible here)
   int use_cluster = 1;
   bool has_graph_rows_narrow() const { return has_graph && csr.max_degree < kNarrow; }
   int64_t build_launches = 0;
@@ -364,7 +364,7 @@ static BfsParams make_params(const b2bfs* h) {
   p.tn.gamma = h->gamma;
   p.tn.huge_min = h->huge_min;
   // graphs of narrow rows only (grids, road-like meshes): the kernel instance with the cluster mode
-  p.tn.cluster = (h->world == 1 && h->use_cluster && h->grid_cluster > 0 && h->has_graph_rows_narrow()) ? 1 : 0;
+  p.tn.cluster = (h->world == 1 && h->use_cluster && h->grid_cluster > 0 && h->has_graph_rows_narrow()) ? h->cluster_size : 0;
   p.tn.xfullpush = h->xfullpush;
   return p;
 }
@@ -484,7 +484,7 @@ int b2bfs_create(b2bfs_t** out, int device) {
     API_CUDA(nullptr, cudaEventCreate(&h->ev1));
     API_CUDA(nullptr, cudaMallocHost(&h->pinned_ctl, sizeof(Control)));
     Status s = search_grid_size(device, &h->grid);
-    if (s.ok()) s = search_cluster_grid_size(h->grid, &h->grid_cluster);
+    if (s.ok()) s = search_cluster_grid_size(h->grid, &h->grid_cluster, &h->cluster_size);
     return s.ok() ? B2BFS_OK : fail(nullptr, s);
   };
   const int rc = create();
@@ -592,7 +592,7 @@ int b2bfs_get_option(const b2bfs_t* h, const char* key, int64_t* value) {
   else if (k == "gamma") *value = h->gamma;
   else if (k == "xfullpush") *value = h->xfullpush;
   else if (k == "huge_min") *value = h->huge_min;
-  else if (k == "cluster") *value = (h->world == 1 && h->use_cluster && h->grid_cluster > 0 && h->has_graph_rows_narrow()) ? 1 : 0;
+  else if (k == "cluster") *value = (h->world == 1 && h->use_cluster && h->grid_cluster > 0 && h->has_graph_rows_narrow()) ? h->cluster_size : 0;
   else if (k == "grid_cluster") *value = h->grid_cluster;
   else if (k == "grid") *value = h->grid;
   else if (k == "gather_parent") *value = h->gather_parent;

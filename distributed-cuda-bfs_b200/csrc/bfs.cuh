@@ -11,7 +11,7 @@ struct BfsParams {
 };
 
 Status search_grid_size(int device, int* grid_out);
-Status search_cluster_grid_size(int plain_grid, int* grid_out);
+Status search_cluster_grid_size(int plain_grid, int* grid_out, int* size_out);
 Status run_fused(const BfsParams& p, int64_t src, int grid, cudaStream_t stream, int64_t* launches);
 Status run_stepwise(const BfsParams& p, int64_t src, int grid, cudaStream_t stream, Control* pinned,
                     int64_t* launches);

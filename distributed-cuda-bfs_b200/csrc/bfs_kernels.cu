@@ -1041,7 +1041,7 @@ __device__ __forceinline__ void trace_mark(Control* c, int& n, int level, int ph
 // round trips (bfs.cu:569-619).
 // ---------------------------------------------------------------------------------------------
 constexpr int kClusterQCap = 2048;                     // per CTA and queue; three queues (ring indexed by level % 3)
-constexpr unsigned kClusterMaxQ = kClusterBlocks * kClusterQCap / 2;   // leave above this many frontier vertices
+constexpr unsigned kClusterMaxQPerBlock = kClusterQCap / 2;   // leave above this many frontier vertices per CTA of the cluster
 constexpr unsigned kClusterEnterQ = 4096;
 struct ClusterQ {
   int32_t q[3][kClusterQCap];
@@ -1078,6 +1078,13 @@ __device__ __forceinline__ Conversion cluster_levels(const BfsParams& p, LoopSta
   __threadfence();
   cluster.sync();
   Conversion cv = kNoConversion;
+#ifdef B2_CLUSTER_PROFILE
+  unsigned long long tp[4] = {0, 0, 0, 0}, t0p = 0;
+#define B2_TP(i) do { unsigned long long _n; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_n)); tp[i] += _n - t0p; t0p = _n; } while (0)
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0p));
+#else
+#define B2_TP(i)
+#endif
   for (;;) {
     const unsigned nxt = cur == 2 ? 0 : cur + 1, spare = nxt == 2 ? 0 : nxt + 1;
     const unsigned cnt = cq->cnt[cur];
@@ -1106,7 +1113,7 @@ __device__ __forceinline__ Conversion cluster_levels(const BfsParams& p, LoopSta
           if (v[k] >= 0 && !((old[k] >> (v[k] & 31)) & 1u)) {
             p.s.depth[v[k]] = level + 1;
             p.s.parent[v[k]] = u;
-            o[k] = cluster.map_shared_rank(cq, ((uint32_t)v[k] ^ ((uint32_t)v[k] >> 9)) % nc);
+            o[k] = cluster.map_shared_rank(cq, ((uint32_t)v[k] ^ ((uint32_t)v[k] >> 9)) & (nc - 1));  // nc is 8 or 16
             pos[k] = atomicAdd(&o[k]->cnt[nxt], 1u);
           }
         }
@@ -1125,15 +1132,22 @@ __device__ __forceinline__ Conversion cluster_levels(const BfsParams& p, LoopSta
     }
     for (int o2 = 16; o2; o2 >>= 1) my_edges += __shfl_xor_sync(0xffffffffu, my_edges, o2);
     if (lane == 0 && my_edges) atomicAdd(&cq->edges[cur], my_edges);
+    B2_TP(0);
     cluster.sync();  // every append has landed, every count and degree sum is final
+    B2_TP(1);
     unsigned nq_t = 0, mf_cur = 0;
     const unsigned cur_t = st.cur_q;  // what the previous level (or the entry) counted
+    {
+      unsigned a[kClusterMaxBlocks], b[kClusterMaxBlocks];
 #pragma unroll
-    for (unsigned r = 0; r < (unsigned)kClusterBlocks; ++r) {
-      if (r < nc) {
-        const ClusterQ* oq = cluster.map_shared_rank(cq, r);
-        nq_t += oq->cnt[nxt];
-        mf_cur += oq->edges[cur];
+      for (unsigned r = 0; r < (unsigned)kClusterMaxBlocks; ++r) {  // all remote loads in flight together
+        const ClusterQ* oq = cluster.map_shared_rank(cq, r < nc ? r : 0);
+        a[r] = *reinterpret_cast<const volatile unsigned int*>(&oq->cnt[nxt]);
+        b[r] = *reinterpret_cast<const volatile unsigned int*>(&oq->edges[cur]);
+      }
+#pragma unroll
+      for (unsigned r = 0; r < (unsigned)kClusterMaxBlocks; ++r) {
+        if (r < nc) { nq_t += a[r]; mf_cur += b[r]; }
       }
     }
     // the degree sum of the NEW frontier is not known yet (its rows are read next level): the mean
@@ -1141,9 +1155,14 @@ __device__ __forceinline__ Conversion cluster_levels(const BfsParams& p, LoopSta
     const unsigned long long mf_est = (unsigned long long)nq_t * (cur_t ? (mf_cur + cur_t - 1) / cur_t : 1u);
     cv = advance(st, p.tn, p.g.n, nq_t, 0, 0, mf_est);
     cur = nxt;
+    B2_TP(2);
     const bool overflow = *reinterpret_cast<volatile unsigned int*>(&ctl->cluster_overflow) != 0;
-    if (st.done || cv != kNoConversion || overflow || nq_t > kClusterMaxQ) break;
+    if (st.done || cv != kNoConversion || overflow || nq_t > kClusterMaxQPerBlock * nc) break;
   }
+#ifdef B2_CLUSTER_PROFILE
+  if (c == 0 && t == 0) printf("[cluster profile, CTA 0 thread 0] levels %d: expand %.1f us, barrier wait %.1f us, totals+advance %.1f us\n",
+                               st.td_levels, tp[0] * 1e-3, tp[1] * 1e-3, tp[2] * 1e-3);
+#endif
   if (st.done) return cv;
   // ---- leave: my part of the frontier -> the global list behind the spills, then all of it -> the
   // ordinary work lists of level st.level
@@ -1211,7 +1230,7 @@ __device__ __forceinline__ void fused_search(BfsParams& p, int64_t src) {
     const unsigned hubs = hub_items(p, st.level);
     if (kCluster && cluster_eligible(st)) {
       ++group_seq;
-      if ((int)blockIdx.x < kClusterBlocks) {
+      if ((int)blockIdx.x < p.tn.cluster) {
         cv = cluster_levels(p, st, stage);
         if (blockIdx.x == 0 && threadIdx.x == 0) {
           p.s.ctl->resume_state = st;
@@ -1225,7 +1244,7 @@ __device__ __forceinline__ void fused_search(BfsParams& p, int64_t src) {
         __syncthreads();
       }
       grid.sync();
-      if ((int)blockIdx.x >= kClusterBlocks) {  // catch up with what the cluster decided
+      if ((int)blockIdx.x >= p.tn.cluster) {  // catch up with what the cluster decided
         const volatile LoopState* rs = &p.s.ctl->resume_state;
         st.level = rs->level; st.mode = rs->mode; st.fb = rs->fb; st.done = rs->done;
         st.prev_nf = rs->prev_nf; st.unexplored = rs->unexplored; st.td_levels = rs->td_levels;
@@ -1311,12 +1330,13 @@ __device__ __forceinline__ void fused_search(BfsParams& p, int64_t src) {
 
 // two instances of the search: the plain one, and one that also holds the cluster mode (chosen per
 // graph by the host: only graphs whose every row is narrower than kNarrow run it, launched in
-// clusters of kClusterBlocks CTAs).  Separate instances keep the extra code's register pressure
+// clusters of Tuning::cluster CTAs).  Separate instances keep the extra code's register pressure
 // away from the power-law path.
 __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(BfsParams p, int64_t src) {
   fused_search<false>(p, src);
 }
-__global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_cluster_kernel(BfsParams p, int64_t src) {
+// (two CTAs per SM are plenty for graphs of narrow rows: the registers go to the level loop instead)
+__global__ void __launch_bounds__(kBlock, 2) bfs_fused_cluster_kernel(BfsParams p, int64_t src) {
   fused_search<true>(p, src);
 }
 
@@ -1601,7 +1621,7 @@ Status run_fused(const BfsParams& p, int64_t src, int grid, cudaStream_t stream,
   BfsParams pp = p;
   int64_t s = src;
   void* args[] = {&pp, &s};
-  if (p.tn.cluster) {  // cooperative AND in clusters of kClusterBlocks CTAs (grid is a multiple of it)
+  if (p.tn.cluster) {  // cooperative AND in clusters (grid is a multiple of the cluster size)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(kBlock);
@@ -1610,7 +1630,7 @@ Status run_fused(const BfsParams& p, int64_t src, int grid, cudaStream_t stream,
     attr[0].id = cudaLaunchAttributeCooperative;
     attr[0].val.cooperative = 1;
     attr[1].id = cudaLaunchAttributeClusterDimension;
-    attr[1].val.clusterDim.x = kClusterBlocks;
+    attr[1].val.clusterDim.x = (unsigned)p.tn.cluster;
     attr[1].val.clusterDim.y = 1;
     attr[1].val.clusterDim.z = 1;
     cfg.attrs = attr;
@@ -1623,28 +1643,41 @@ Status run_fused(const BfsParams& p, int64_t src, int grid, cudaStream_t stream,
   return Status();
 }
 
-// Largest grid of the search kernel that is co-resident when launched in clusters, 0 if the device
-// (or this driver) cannot run it that way or would lose more than a tenth of the plain grid.
-Status search_cluster_grid_size(int plain_grid, int* grid_out) {
+// Cluster size and grid for the cluster-mode kernel: 16 CTAs per cluster where the device admits it
+// (a non-portable size, opt-in), else 8; the grid is the largest co-resident multiple.  *size_out = 0
+// if the device (or this driver) cannot run the kernel in clusters on at least a quarter of the plain grid.
+Status search_cluster_grid_size(int plain_grid, int* grid_out, int* size_out) {
   *grid_out = 0;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(plain_grid / kClusterBlocks * kClusterBlocks);
-  cfg.blockDim = dim3(kBlock);
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = kClusterBlocks;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  int clusters = 0;
-  if (cudaOccupancyMaxActiveClusters(&clusters, (const void*)bfs_fused_cluster_kernel, &cfg) != cudaSuccess) {
-    cudaGetLastError();
-    return Status();
+  *size_out = 0;
+  for (int size = kClusterMaxBlocks; size >= 8 && *size_out == 0; size /= 2) {
+    if (size > 8 &&
+        cudaFuncSetAttribute((const void*)bfs_fused_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+      cudaGetLastError();
+      continue;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(plain_grid / size * size);
+    cfg.blockDim = dim3(kBlock);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)size;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&clusters, (const void*)bfs_fused_cluster_kernel, &cfg) != cudaSuccess) {
+      cudaGetLastError();
+      continue;
+    }
+    int g = clusters * size;
+    if (g > plain_grid / size * size) g = plain_grid / size * size;
+    // graphs that run this kernel have little parallel work per level: a quarter of the plain grid is plenty
+    if (g * 4 >= plain_grid) {
+      *grid_out = g;
+      *size_out = size;
+    }
   }
-  int g = clusters * kClusterBlocks;
-  if (g > plain_grid / kClusterBlocks * kClusterBlocks) g = plain_grid / kClusterBlocks * kClusterBlocks;
-  if (g * 10 >= plain_grid * 9) *grid_out = g;
   return Status();
 }
 

@@ -16,7 +16,7 @@ constexpr int kWarpsPerBlock = kBlock / 32;
 constexpr int kSMs = 148;                // B200: 2 dies x 74 SMs; grids are sized in multiples of it
 constexpr int kNarrow = 32;              // rows narrower than this are gathered 32 at a time by one warp
 constexpr int kChunk = 128;              // wider rows are cut into work items of this many entries
-constexpr int kClusterBlocks = 8;        // portable cluster size; 592 = 8 x 74 CTAs
+constexpr int kClusterMaxBlocks = 16;     // cluster size of the cluster-mode kernel: 16 where the device admits it, else 8 (portable)
 constexpr int kCtaChunk = 2048;          // rows of at least Tuning::huge_min entries: items of this many entries, one CTA
                                          // each, staged into shared memory by a bulk asynchronous copy (TMA, 1-D)
 
@@ -163,7 +163,7 @@ struct Tuning {
   int alpha;                 // top-down -> bottom-up when m_f > m_u / alpha
   int beta;                  // bottom-up -> top-down when n_f < n / beta
   int gamma;                 // claim-only top-down level + forced switch when m_f * gamma > m_u / alpha (0: never)
-  int cluster;               // the search kernel was launched in clusters of kClusterBlocks CTAs (small frontiers then
+  int cluster;               // CTAs per cluster the search kernel was launched with, 0 = no clusters (small frontiers then
                              // run inside cluster 0: queues in distributed shared memory, hardware cluster barrier)
   int huge_min;              // rows of at least this many entries go to the CTA-level bin (0: bin off)
   int xfullpush;              // peer-memory engine: 1 = push whole frontier slices, 0 = only the 16-byte groups that changed
