@@ -196,6 +196,31 @@ def test_large_graph_properties(b2, gpu):
         _check_search(b2, gpu, g, int(r))
 
 
+def test_full_16m_vertex_grid_from_corner_and_centre(b2):
+    """BASELINE configs[3]: the 4096 x 4096 grid (16.7 M vertices, thousands of levels).  From the corner
+    (8191 levels, the longest search the graph has) and from the centre, every one of the n depths equals
+    the reference's own bfsCPU where oracle/_ref is present (else the restatement); the cluster-mode
+    kernel runs all of it, the plain kernel (option cluster = 0) must agree."""
+    n, s, d = oracle.generate_edges(oracle.GEN_GRID, 24, 0, 0)
+    g = oracle.build_csr_parallel(n, s, d)
+    use_ref = oracle.ref_available()
+    if use_ref:
+        oracle.ref_set_graph(g)
+    side = 4096
+    with b2.Bfs(0) as h:
+        h.generate(b2.KIND_GRID, 24, 0, 0)
+        assert h.num_vertices == n == side * side and h.get_option("max_degree") == 4
+        for root, levels in ((0, 2 * side - 1), (side // 2 * side + side // 2, side + 1)):
+            want = oracle.ref_bfs_cpu(root, n)[0] if use_ref else oracle.bfs_serial(g, root)
+            for cluster in (1, 0):
+                h.set_option("cluster", cluster)
+                depth, parent, st = h.run(root, want_parent=True)
+                bad = oracle.check_output(depth, want)
+                assert bad == -1, f"root {root} cluster {cluster}: vertex {bad} got {depth[bad]} want {want[bad]}"
+                assert st["levels"] == levels and st["reached_vertices"] == n
+                assert oracle.validate_tree(g, root, depth, parent) == (0, -1)
+
+
 def test_boundary_errors(b2, tmp_path):
     with b2.Bfs(0) as h:
         with pytest.raises(b2.B2BfsError) as e:
