@@ -566,7 +566,7 @@ def multi_gpu_parity(args, kind, n, roots, depths, line):
     # bfsCPU itself on as many of those roots as the budget allows (the reference's own code while
     # 2m < 2^31, its 64-bit port beyond)
     left = args.cpu_budget - (time.perf_counter() - t_start)
-    est_build = 4.0 * (m / 2**26)  # ~4 s per 2^26 tuples on 8 cores, measured
+    est_build = 4.0 * (m / 2**26) * 8.0 / max(os.cpu_count() or 8, 1)  # ~4 s per 2^26 tuples on 8 cores, measured
     if cpu_graph_bytes(n, m) < 0.8 * mem_available_bytes() and est_build < left:
         cpu = CpuReference(n, src, dst, args.scale)
         del src, dst
