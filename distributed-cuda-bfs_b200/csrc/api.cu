@@ -26,7 +26,7 @@ struct b2bfs {
   std::string err;
   // options
   int dedup = 1, mode = B2BFS_MODE_DIRECTION_OPT, engine = B2BFS_ENGINE_FUSED;
-  int alpha = 14, beta = 24, gamma = 2000, huge_min = 4096, xfullpush = 0, keep_edges = 1, gather_parent = 1, hub_first = 1, directed = 0;
+  int alpha = 14, beta = 24, gamma = 2000, huge_min = 0, xfullpush = 0, keep_edges = 1, gather_parent = 1, hub_first = 1, directed = 0;
   // graph
   bool has_graph = false;
   int64_t n = 0, m = 0;
@@ -362,7 +362,7 @@ static BfsParams make_params(const b2bfs* h) {
   p.tn.alpha = h->alpha;
   p.tn.beta = h->beta;
   p.tn.gamma = h->gamma;
-  p.tn.huge_min = h->huge_min;
+  p.tn.huge_min = (!multi && h->sv.hugeq[0]) ? h->huge_min : 0;  // no hub lists, no hub bin
   // graphs of narrow rows only (grids, road-like meshes): the kernel instance with the cluster mode
   p.tn.cluster = (h->world == 1 && h->use_cluster && h->grid_cluster > 0 && h->has_graph_rows_narrow()) ? h->cluster_size : 0;
   p.tn.xfullpush = h->xfullpush;

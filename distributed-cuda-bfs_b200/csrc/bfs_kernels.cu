@@ -74,26 +74,16 @@ __device__ __forceinline__ unsigned long long ld_volatile(const unsigned long lo
   return *reinterpret_cast<const volatile unsigned long long*>(p);
 }
 
-// where hub rows go (the CTA-level bin); min == 0 switches the bin off
-struct HubOut {
-  int2* q;
-  unsigned int* count;
-  int64_t min;
-};
-__device__ __forceinline__ HubOut hub_out(const BfsParams& p, int level_of_items) {
-  HubOut h;
-  h.q = p.s.hugeq[level_of_items & 1];
-  h.count = &p.s.ctl->slot[level_of_items & 3].huge_count;
-  h.min = (h.q && p.g.world == 1) ? (int64_t)p.tn.huge_min : 0;
-  return h;
-}
-
-// Route a newly discovered vertex of degree d to the next level's work lists (lane-local).
-__device__ __forceinline__ void route_vertex(WarpStage& sg, int32_t v, int64_t d, const HubOut& hub) {
-  if (hub.min > 0 && d >= hub.min) {  // a handful of vertices per search: one tail atomic each is fine
+// Route a newly discovered vertex of degree d to the work lists of level `items_level` (lane-local).
+// Hub rows (the CTA-level bin; Tuning::huge_min == 0 switches it off - the host sets 0 whenever the
+// hub lists do not exist) are rare: everything they need is fetched inside their branch, so the
+// common path carries no extra registers.
+__device__ __forceinline__ void route_vertex(WarpStage& sg, int32_t v, int64_t d, const BfsParams& p, int items_level) {
+  if (p.tn.huge_min > 0 && d >= p.tn.huge_min) {  // a handful of vertices per search: one tail atomic each is fine
     const unsigned items = (unsigned)((d + kCtaChunk - 1) / kCtaChunk);
-    const unsigned base = atomicAdd(hub.count, items);
-    for (unsigned c = 0; c < items; ++c) hub.q[base + c] = make_int2(v, (int)c);
+    const unsigned base = atomicAdd(&p.s.ctl->slot[items_level & 3].huge_count, items);
+    int2* hq = p.s.hugeq[items_level & 1];
+    for (unsigned c = 0; c < items; ++c) hq[base + c] = make_int2(v, (int)c);
   } else if (d < kNarrow) {
     sg.narrow[atomicAdd(&sg.ncnt, 1)] = v;
   } else {
@@ -211,11 +201,10 @@ __device__ __forceinline__ void phase_init(const BfsParams& p, int64_t src) {
       c->slot[k].bu_cursor = 0;
     }
     const int64_t deg = src >= 0 ? p.g.rowptr[src + 1] - p.g.rowptr[src] : 0;  // src < 0: another rank owns it
-    const HubOut hub = hub_out(p, 0);
     if (src < 0) {
-    } else if (hub.min > 0 && deg >= hub.min) {
+    } else if (p.tn.huge_min > 0 && deg >= p.tn.huge_min) {
       const unsigned items = (unsigned)((deg + kCtaChunk - 1) / kCtaChunk);
-      for (unsigned k = 0; k < items; ++k) hub.q[k] = make_int2((int)src, (int)k);
+      for (unsigned k = 0; k < items; ++k) p.s.hugeq[0][k] = make_int2((int)src, (int)k);
       c->slot[0].huge_count = items;
     } else if (deg < kNarrow) {
       p.s.queue[0][0] = (int32_t)src;
@@ -238,7 +227,7 @@ __host__ __device__ inline LoopState initial_state(const BfsParams& p, int64_t s
   st.mode = 0;
   st.fb = 0;
   st.done = 0;
-  const bool hub = p.s.hugeq[0] && p.g.world == 1 && p.tn.huge_min > 0 && src_degree >= p.tn.huge_min;
+  const bool hub = p.tn.huge_min > 0 && src_degree >= p.tn.huge_min;
   const bool wide = src_degree >= kNarrow && !hub;
   st.cur_q = (wide || hub) ? 0u : 1u;
   st.cur_wide = wide ? (unsigned)((src_degree + kChunk - 1) / kChunk) : 0u;
@@ -342,7 +331,7 @@ __device__ __forceinline__ void hub_issue(const BfsParams& p, HubStage* hs, int 
 template <bool kMulti>
 __device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpStage& sg, RemoteStage* rs,
                                           const int32_t (&v)[4], const int32_t (&u)[4], const bool (&valid)[4],
-                                          unsigned long long& edges_acc, bool mark, bool claim_only, const HubOut& hub) {
+                                          unsigned long long& edges_acc, bool mark, bool claim_only) {
   uint32_t word[4];
   bool c[4], local[4];
   int32_t vl[4];
@@ -397,7 +386,7 @@ __device__ __forceinline__ void td_visit4(const BfsParams& p, int level, WarpSta
         p.s.depth[vl[k]] = level + 1;
         p.s.parent[vl[k]] = u[k];
         edges_acc += (unsigned long long)d[k];
-        route_vertex(sg, vl[k], d[k], hub);
+        route_vertex(sg, vl[k], d[k], p, level + 1);
         // the next level will most likely run bottom-up: leave the frontier bit behind now and
         // save the queue->bitmap pass and its grid-wide barrier
         if (mark) atomicOr(&p.s.bitmap[0][(uint32_t)vl[k] >> 5], 1u << (vl[k] & 31));
@@ -426,7 +415,6 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
 
   RemoteStage* rst = kMulti ? &rstage[threadIdx.x >> 5] : nullptr;
   const int32_t vbase = (int32_t)p.g.vbase;
-  const HubOut hub = hub_out(p, level + 1);
   if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
   if (kMulti && lane == 0) rst->cnt = 0;
   if (bid == 0 && threadIdx.x == 0) {  // recycle the slot two levels ahead
@@ -456,7 +444,7 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
           const int32_t uu[4] = {u + vbase, u + vbase, u + vbase, u + vbase};
           const int64_t e = a0 + idx;
           const bool valid[4] = {e >= rs, e + 1 >= rs && e + 1 < re, e + 2 >= rs && e + 2 < re, e + 3 >= rs && e + 3 < re};
-          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only, hub);
+          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only);
         }
         stage_flush(sg, ns, nq, nwq, false);
       }
@@ -506,7 +494,7 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
           valid[j] = k < total;
           v[j] = valid[j] ? __ldg(p.g.col + ors + (k - oe)) : 0;
         }
-        td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only, hub);
+        td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only);
         stage_flush(sg, ns, nq, nwq, false);
         if (kMulti) remote_flush(p, *rst, false);
       }
@@ -524,7 +512,7 @@ __device__ __forceinline__ void phase_top_down(const BfsParams& p, const LoopSta
           const int32_t uu[4] = {u + vbase, u + vbase, u + vbase, u + vbase};
           const bool valid[4] = {base >= rs, base + 1 >= rs && base + 1 < re, base + 2 >= rs && base + 2 < re,
                                  base + 3 >= rs && base + 3 < re};
-          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only, hub);
+          td_visit4<kMulti>(p, level, sg, rst, v, uu, valid, edges_acc, mark, claim_only);
         }
         stage_flush(sg, ns, nq, nwq, false);
         if (kMulti) remote_flush(p, *rst, false);
@@ -548,7 +536,6 @@ __device__ __forceinline__ void phase_apply_remote(const BfsParams& p, const Loo
   int2* nwq = p.s.wideq[(level + 1) & 1];
   LevelSlot* ns = &p.s.ctl->slot[(level + 1) & 3];
   WarpStage& sg = stage[threadIdx.x >> 5];
-  const HubOut hub = hub_out(p, level + 1);
   if (lane_id() == 0) { sg.ncnt = 0; sg.wcnt = 0; }
   __syncwarp();
   unsigned long long edges_acc = 0;
@@ -572,7 +559,7 @@ __device__ __forceinline__ void phase_apply_remote(const BfsParams& p, const Loo
         } else {
           const int64_t d = __ldg(p.g.rowptr + vl + 1) - __ldg(p.g.rowptr + vl);
           edges_acc += (unsigned long long)d;
-          route_vertex(sg, vl, d, hub);
+          route_vertex(sg, vl, d, p, level + 1);
         }
         if (mark) atomicOr(&p.s.bitmap[0][w], bit);
       }
@@ -871,7 +858,6 @@ __device__ __forceinline__ void phase_bitmap_to_queue(const BfsParams& p, const 
   int32_t* q = p.s.queue[st.level & 1];
   int2* wq = p.s.wideq[st.level & 1];
   LevelSlot* cs = &p.s.ctl->slot[st.level & 3];
-  const HubOut hub = hub_out(p, st.level);
   const unsigned lane = lane_id();
   WarpStage& sg = stage[threadIdx.x >> 5];
   if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
@@ -895,7 +881,7 @@ __device__ __forceinline__ void phase_bitmap_to_queue(const BfsParams& p, const 
           const int b = __ffs(bits) - 1;
           bits &= bits - 1;
           const int64_t v = w * 32 + b;
-          route_vertex(sg, (int32_t)v, __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v), hub);
+          route_vertex(sg, (int32_t)v, __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v), p, st.level);
         }
       }
       stage_flush(sg, cs, q, wq, false);
@@ -909,6 +895,12 @@ __device__ __forceinline__ void phase_bitmap_to_queue(const BfsParams& p, const 
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock) search_init_kernel(BfsParams p, int64_t src) { phase_init(p, src); }
 __global__ void __launch_bounds__(kBlock) top_down_kernel(BfsParams p, LoopState st, bool claim_only) {
+  __shared__ WarpStage stage[kWarpsPerBlock];
+  phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x, nullptr, claim_only, claim_only);
+}
+// the instance with the hub bin (its 16 KiB of staging buffers stay out of the plain kernels: shared
+// memory taken from every CTA is L1 taken from the bitmap probes)
+__global__ void __launch_bounds__(kBlock) top_down_hub_kernel(BfsParams p, LoopState st, bool claim_only) {
   __shared__ WarpStage stage[kWarpsPerBlock];
   __shared__ HubStage hub;
   if (threadIdx.x == 0) hub_stage_init(&hub);
@@ -1184,8 +1176,7 @@ __device__ __forceinline__ Conversion cluster_levels(const BfsParams& p, LoopSta
   const unsigned total = *reinterpret_cast<volatile unsigned int*>(&ctl->dump_count);
   {
     LevelSlot* cs = &ctl->slot[st.level & 3];
-    const HubOut hub = hub_out(p, st.level);
-    WarpStage& sg = stage[t >> 5];
+      WarpStage& sg = stage[t >> 5];
     if (lane == 0) { sg.ncnt = 0; sg.wcnt = 0; }
     __syncwarp();
     const unsigned stride = nc * kBlock;
@@ -1193,7 +1184,7 @@ __device__ __forceinline__ Conversion cluster_levels(const BfsParams& p, LoopSta
       const unsigned i = i0 + c * kBlock + t;
       if (i < total) {
         const int32_t v = __ldcg(tmp + i);
-        route_vertex(sg, v, __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v), hub);
+        route_vertex(sg, v, __ldg(p.g.rowptr + v + 1) - __ldg(p.g.rowptr + v), p, st.level);
       }
       stage_flush(sg, cs, p.s.queue[st.level & 1], p.s.wideq[st.level & 1], false);
     }
@@ -1207,11 +1198,15 @@ __device__ __forceinline__ unsigned hub_items(const BfsParams& p, int level) {
   return p.s.hugeq[0] ? ld_volatile(&p.s.ctl->slot[level & 3].huge_count) : 0u;
 }
 
-template <bool kCluster>
+template <bool kCluster, bool kHub>
 __device__ __forceinline__ void fused_search(BfsParams& p, int64_t src) {
   __shared__ WarpStage stage[kWarpsPerBlock];
-  __shared__ HubStage hub;
-  if (threadIdx.x == 0) hub_stage_init(&hub);
+  HubStage* hs = nullptr;
+  if constexpr (kHub) {
+    __shared__ HubStage hub;
+    if (threadIdx.x == 0) hub_stage_init(&hub);
+    hs = &hub;
+  }
   __syncthreads();
   cg::grid_group grid = cg::this_grid();
   if (blockIdx.x == 0 && threadIdx.x == 0) p.s.ctl->trace_len = 0;
@@ -1294,7 +1289,7 @@ __device__ __forceinline__ void fused_search(BfsParams& p, int64_t src) {
       const int ph = st.mode == 0 ? 1 : 2;
       marked = st.mode == 0 && p.tn.mode == B2BFS_MODE_DIRECTION_OPT && st.bu_levels == 0 && st.level >= 1;
       const bool claim = claim_only_level(st, p.tn);  // implies marked
-      if (st.mode == 0) phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x, nullptr, marked, claim, &hub);
+      if (st.mode == 0) phase_top_down<false>(p, st, stage, blockIdx.x, gridDim.x, nullptr, marked, claim, hs);
       else phase_bottom_up(p, st, stage);
       grid.sync();
       trace_mark(p.s.ctl, ntrace, st.level, claim ? 6 : ph);
@@ -1333,11 +1328,18 @@ __device__ __forceinline__ void fused_search(BfsParams& p, int64_t src) {
 // clusters of Tuning::cluster CTAs).  Separate instances keep the extra code's register pressure
 // away from the power-law path.
 __global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_kernel(BfsParams p, int64_t src) {
-  fused_search<false>(p, src);
+  fused_search<false, false>(p, src);
+}
+// ... and the instance with the CTA-level hub bin (option huge_min > 0).  Its two 8 KiB staging
+// buffers cost every CTA shared memory, i.e. every SM 64 KiB of L1: measured against the plain
+// instance the bin loses more through that than bulk-copy staging wins (profiles/r2), so it is its
+// own kernel and off by default.
+__global__ void __launch_bounds__(kBlock, B2_FUSED_MIN_BLOCKS) bfs_fused_hub_kernel(BfsParams p, int64_t src) {
+  fused_search<false, true>(p, src);
 }
 // (two CTAs per SM are plenty for graphs of narrow rows: the registers go to the level loop instead)
 __global__ void __launch_bounds__(kBlock, 2) bfs_fused_cluster_kernel(BfsParams p, int64_t src) {
-  fused_search<true>(p, src);
+  fused_search<true, false>(p, src);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1637,7 +1639,8 @@ Status run_fused(const BfsParams& p, int64_t src, int grid, cudaStream_t stream,
     cfg.numAttrs = 2;
     B2_CUDA(cudaLaunchKernelExC(&cfg, (const void*)bfs_fused_cluster_kernel, args));
   } else {
-    B2_CUDA(cudaLaunchCooperativeKernel((const void*)bfs_fused_kernel, dim3(grid), dim3(kBlock), args, 0, stream));
+    const void* kernel = p.tn.huge_min > 0 ? (const void*)bfs_fused_hub_kernel : (const void*)bfs_fused_kernel;
+    B2_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(grid), dim3(kBlock), args, 0, stream));
   }
   if (launches) *launches += 1;
   return Status();
@@ -1715,7 +1718,8 @@ Status run_stepwise(const BfsParams& p, int64_t src, int grid, cudaStream_t stre
       fprintf(stderr, "[b2bfs] level %d %s frontier q=%u wide=%u unexplored=%llu\n", st.level,
               st.mode ? "bottom-up" : "top-down", st.cur_q, st.cur_wide, st.unexplored);
     const bool claim = claim_only_level(st, p.tn);
-    if (st.mode == 0) top_down_kernel<<<grid, kBlock, 0, stream>>>(p, st, claim);
+    if (st.mode == 0 && p.tn.huge_min > 0) top_down_hub_kernel<<<grid, kBlock, 0, stream>>>(p, st, claim);
+    else if (st.mode == 0) top_down_kernel<<<grid, kBlock, 0, stream>>>(p, st, claim);
     else bottom_up_kernel<<<grid, kBlock, 0, stream>>>(p, st);
     ++nl;
     B2_CUDA(cudaMemcpyAsync(pinned, p.s.ctl, sizeof(Control), cudaMemcpyDeviceToHost, stream));
