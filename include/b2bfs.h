@@ -94,7 +94,11 @@ int b2bfs_comm_unique_id(void* out128);
  * unexplored entries / alpha only claims vertices and forces the switch to bottom-up; 0 = never),
  * "keep_edges" (1: keep the input tuples resident for b2bfs_copy_edges), "directed" (1: a tuple
  * "u v" is the single arc u -> v, as the reference's stdin reader builds it, bfs.cu:901, instead of
- * an undirected edge, bfs.cu:860-861; such graphs are searched top-down only, on one GPU).
+ * an undirected edge, bfs.cu:860-861; such graphs are searched top-down only, on one GPU),
+ * "huge_min" (0, the default: off; >= 4096: rows of at least that many entries are expanded by whole
+ * CTAs out of shared memory, filled by bulk asynchronous copies - a separate kernel instance),
+ * "cluster" (1: graphs whose every row has fewer than 32 entries - grids, road-like meshes - run the
+ * kernel instance that keeps small frontiers in distributed shared memory; 0: never).
  * Replaces the reference's compile-time switches (#define DeviceNum, commented call sites in main,
  * bfs.cu:19, 805-819). */
 int b2bfs_set_option(b2bfs_t* h, const char* key, int64_t value);
