@@ -301,6 +301,11 @@ def run_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     dev = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(dev)
+    # stdout carries ONE line, the JSON: whatever libraries write to file descriptor 1 meanwhile (NCCL
+    # prints a version banner there under NCCL_DEBUG=VERSION) goes to stderr instead
+    sys.stdout.flush()
+    stdout_fd = os.dup(1)
+    os.dup2(2, 1)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -537,6 +542,9 @@ def run_ours(args):
         my_slice = None
         shared.free()
     h.close()
+    sys.stdout.flush()
+    os.dup2(stdout_fd, 1)
+    os.close(stdout_fd)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:
