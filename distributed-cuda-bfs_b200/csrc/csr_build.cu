@@ -42,8 +42,9 @@ Status generate_edges_device(int kind, int scale, int ef, uint64_t seed, int64_t
 // ---------------------------------------------------------------------------------------------
 // tuples -> keys.  Every tuple (u,v) yields (u -> v) and (v -> u), as bfs.cu:860-861 does; a
 // self-loop yields two identical keys, which keeps orig_deg equal to the reference's edgesSize.
-// Rows outside [row_begin, row_end) are not this rank's: `keys` then receives only owned entries
-// through a warp-aggregated append (cursor != nullptr).  bad_flag is raised for ids outside [0,n).
+// (One GPU.  Several ranks expand their share of the tuples with owner_keys_kernel below; the
+// cursor path here - keep only rows in [row_begin, row_end) - is the round-1 scheme, kept for callers
+// that hold all tuples.)  bad_flag is raised for ids outside [0,n).
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock) expand_edges_kernel(const int32_t* __restrict__ src,
                                                               const int32_t* __restrict__ dst, int64_t m, int64_t n,
@@ -103,19 +104,6 @@ __global__ void __launch_bounds__(kBlock) degree_count_kernel(const int32_t* __r
       atomicAdd(&degc[v], 1u);
     }
   }
-}
-
-__global__ void __launch_bounds__(kBlock) count_owned_kernel(const int32_t* __restrict__ src,
-                                                             const int32_t* __restrict__ dst, int64_t m,
-                                                             int64_t row_begin, int64_t row_end,
-                                                             unsigned long long* total) {
-  unsigned long long c = 0;
-  for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < m; i += (int64_t)gridDim.x * kBlock) {
-    const int64_t u = src[i], v = dst[i];
-    c += (u >= row_begin && u < row_end) + (v >= row_begin && v < row_end);
-  }
-  for (int o = 16; o; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
-  if ((threadIdx.x & 31) == 0 && c) atomicAdd(total, c);
 }
 
 // ---------------------------------------------------------------------------------------------
