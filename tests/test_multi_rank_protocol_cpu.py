@@ -164,3 +164,73 @@ def test_partition_arithmetic():
         for v in (0, n - 1, n // 2):
             r = v // part
             assert ranges[r][0] <= v < ranges[r][1]
+
+
+# ---------------------------------------------------------------------------------------------
+# construction by owner exchange (api.cu build_partitioned / csr_build.cu owner_keys_kernel): every
+# rank holds m/k of the tuples, buckets the two entries of each tuple by the rank that owns their
+# row, the buckets are exchanged, and a rank keeps exactly the rows of the serial CSR that it owns
+# ---------------------------------------------------------------------------------------------
+def tuple_share(m, rank, world):
+    first = m * rank // world
+    return first, m * (rank + 1) // world - first
+
+
+def exchange_worker(rank, world, port, results):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ok = 0
+        for kind, scale, ef, seed in ((oracle.GEN_KRON, 10, 8, 1), (oracle.GEN_RMAT, 9, 16, 2), (oracle.GEN_GRID, 8, 0, 0),
+                                      (oracle.GEN_RMAT, 3, 1, 5)):  # the last one: fewer tuples than some ranks' share needs
+            n, s, d = oracle.generate_edges(kind, scale, ef, seed)
+            g = oracle.build_csr(n, s, d)  # the reference's rows (multigraph), for every vertex
+            m = len(s)
+            part, ranges = partition(n, world)
+            lo, hi = ranges[rank]
+            first, cnt = tuple_share(m, rank, world)
+            ls, ld = s[first:first + cnt].astype(np.int64), d[first:first + cnt].astype(np.int64)
+            # degree of every vertex from the local tuples, summed over ranks (the hub-first class needs it)
+            deg = torch.from_numpy(np.bincount(ls, minlength=n) + np.bincount(ld, minlength=n))
+            dist.all_reduce(deg)
+            assert np.array_equal(deg.numpy(), g.sizes.astype(np.int64))
+            # both entries of every local tuple, bucketed by owner of the row
+            rows = np.concatenate([ls, ld]); nbrs = np.concatenate([ld, ls])
+            owner = rows // part
+            send = [np.stack([rows[owner == r], nbrs[owner == r]], 1) for r in range(world)]
+            counts = [None] * world
+            dist.all_gather_object(counts, [len(x) for x in send])      # the k x k count matrix
+            assert sum(counts[rank]) == 2 * cnt
+            recv = [None] * world
+            for r in range(world):                                      # all-to-all-v of the buckets
+                out = [None] * world if r == rank else None
+                dist.gather_object(send[r], out, dst=r)
+                if r == rank:
+                    recv = out
+            mine = np.concatenate([x.reshape(-1, 2) for x in recv]) if recv else np.zeros((0, 2), np.int64)
+            assert len(mine) == sum(c[rank] for c in counts)
+            assert ((mine[:, 0] >= lo) & (mine[:, 0] < hi)).all() if len(mine) else True
+            # what arrived is exactly this rank's rows of the serial CSR, as multisets
+            for v in range(lo, hi):
+                got = np.sort(mine[mine[:, 0] == v, 1])
+                want = np.sort(g.adj[g.offsets[v]:g.offsets[v] + g.sizes[v]])
+                assert np.array_equal(got, want), (rank, v)
+            ok += 1
+        results[rank] = ok
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,port", [(2, 29741), (3, 29743)])
+def test_owner_exchange_builds_each_ranks_rows(world, port):
+    mgr = mp.Manager()
+    results = mgr.dict()
+    mp.spawn(exchange_worker, args=(world, port, results), nprocs=world, join=True)
+    assert len(results) == world and all(v == 4 for v in results.values())
+
+
+def test_tuple_shares_cover_every_tuple_once():
+    for m, k in ((0, 2), (1, 8), (5, 8), (1000, 3), (1 << 33, 8)):
+        shares = [tuple_share(m, r, k) for r in range(k)]
+        assert shares[0][0] == 0 and sum(c for _, c in shares) == m
+        assert all(a[0] + a[1] == b[0] for a, b in zip(shares, shares[1:]))
